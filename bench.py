@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""Benchmark of the B200 K-Means Lloyd path (BASELINE.json metric: Lloyd point-iterations/s at
+N=100M, D=128, K=1024).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c4]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one Lloyd iteration over the whole (sharded) batch: assignment + per-cluster
+accumulation on every rank, one NCCL all-reduce of the K*D+K+2 partial doubles (N > 1), centroid
+update.  Points are generated on the device and stay resident (the reference keeps them in
+`tf.Variable`s, scripts/distribuitedClustering.py:217); N total rows are split over the ranks by
+the reference's array_split rule (:184), so the total work is fixed ("strong" scaling).
+
+One JSON line is printed by rank 0; see DESIGN.md section "Measurement" for every key.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "lloyd_point_iterations_per_sec"
+UNIT = "point-iterations/s"
+CONFIGS = {
+    # name: (N total, D, K, kind)
+    "c1": (1_000_000, 2, 8, "blobs"),
+    "c2": (3840 * 2160, 3, 16, "image"),
+    "c3": (10_000_000, 32, 256, "blobs"),
+    "c4": (100_000_000, 128, 1024, "blobs"),
+    "c5": (1_000_000_000, 64, 4096, "blobs"),
+}
+SEED = 123128          # the seed the reference logs (scripts/new_experiment.py:56)
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": float(p["hbm_gbs"]), "tflops": float(p.get("bf16_tflops_sustained", p["bf16_tflops"])),
+                "tflops_burst": float(p["bf16_tflops"]), "source": "measured"}
+    # /opt/skills/guides/B200_PROFILING.md fallback figures
+    return {"hbm_gbs": 6650.0, "tflops": 1400.0, "tflops_burst": 1590.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period_s: float = 0.1):
+        self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
+        self._stop = threading.Event()
+        self._period = period_s
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as e:        # no NVML here: report that instead of inventing clocks
+            self.error = repr(e)
+        self._t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        nv = self._nv
+        names = {
+            "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
+            "hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+            "hw_power_brake_slowdown": getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80),
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(self._period)
+
+    def start(self):
+        if self.ok:
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self.ok:
+            self._t.join(timeout=2)
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "NVML unavailable"}
+        return {"sm_mhz": int(statistics.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU baseline / reference arm: the oracle port of the reference's CPU path, on the host cores
+# ----------------------------------------------------------------------------------------------
+def cpu_reference_step_factory(D, K, kind, sample_rows):
+    """One bounded Lloyd iteration of the oracle (float64 restatement of reference :221-263) on a
+    `sample_rows` sample of the same workload, using all host threads BLAS gives it."""
+    import oracle
+
+    pkg = importlib.import_module("tensorflow-distributed-clustering_b200")
+    if kind == "image":
+        side = int(np.sqrt(sample_rows / (16 / 9)))
+        X = pkg.datagen.image_numpy(side, side * 16 // 9, SEED)
+        C = pkg.datagen.kmeanspp_init(X, K, SEED).astype(np.float64)
+    else:
+        X, _ = pkg.datagen.blobs_numpy(sample_rows, D, K, SEED)
+        C = X[:K].astype(np.float64)
+    form = "gemm" if K * D > 4096 else "diff"
+    state = {"C": C}
+
+    def step():
+        it = oracle.lloyd_iteration(X, state["C"], n_shards=1, form=form)
+        state["C"] = it["centroids"]
+        return it["inertia"]
+
+    return step, X.shape[0], form
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference_arm(args, cfg_name):
+    N, D, K, kind = CONFIGS[cfg_name]
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    per_step_flops = 8e10                      # ~ a few seconds of host BLAS per step
+    sample = int(min(N, max(4096, per_step_flops / (2.0 * K * D))))
+    step, rows, form = cpu_reference_step_factory(D, K, kind, sample)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = rows * args.steps / dt
+    cores = host_cores()
+    sample_desc = f"{rows} rows of the {cfg_name} workload (D={D}, K={K}), float64 {form}-form oracle, {args.steps} iterations"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": workload_name(cfg_name), "N": N, "D": D, "K": K,
+                   "note": "TensorFlow is not installable here; the reference's CPU path is timed as its float64 NumPy restatement (oracle/)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_name(cfg_name):
+    N, D, K, kind = CONFIGS[cfg_name]
+    what = "synthetic 4K RGB image" if kind == "image" else "synthetic Gaussian blobs"
+    return f"{cfg_name}: {what} N={N} D={D} K={K} fp32, one Lloyd iteration per step"
+
+
+# ----------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
+    ap.add_argument("--rows", type=int, default=0, help="override total rows (debugging only; marks the line invalid)")
+    ap.add_argument("--path", default="auto", choices=["auto", "small", "simt", "tc"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+
+    if args.impl == "reference":
+        run_reference_arm(args, args.config)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    pkg = importlib.import_module("tensorflow-distributed-clustering_b200")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs CUDA devices (B200); the product has no CPU fallback")
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    N, D, K, kind = CONFIGS[args.config]
+    if args.rows:
+        N = args.rows
+    r0, r1 = pkg.shard_ranges(N, world)[rank]
+    n_local = r1 - r0
+
+    # ---- synthetic data, generated on the device, resident for the whole run ----
+    if kind == "image":
+        X = pkg.datagen.image_torch(2160, 3840, SEED, dev)[r0:r1].contiguous()
+        C0 = pkg.datagen.kmeanspp_init(X[:: max(1, n_local // 65536)].cpu().numpy(), K, SEED) if rank == 0 else None
+    else:
+        X, _ = pkg.datagen.blobs_torch(n_local, D, K, SEED + rank, dev)
+        C0 = X[:K].cpu().numpy() if rank == 0 else None
+    c0_t = torch.from_numpy(C0).to(dev) if rank == 0 else torch.empty((K, D), dtype=torch.float32, device=dev)
+    if world > 1:
+        dist.broadcast(c0_t, 0)
+    C0 = c0_t.cpu().numpy()
+
+    shard = pkg.LloydShard(n_local, D, K, dev, path=args.path)
+    shard.bind_points(X)
+    shard.set_centroids(C0)
+    shard.enable_profile(True)
+    torch.cuda.synchronize(dev)
+
+    def one_step():
+        shard.accumulate()
+        if world > 1:
+            dist.all_reduce(shard.partials)
+        shard.update()
+
+    for _ in range(args.warmup):
+        one_step()
+    torch.cuda.synchronize(dev)
+    shard.phase_ms()                                   # reset the phase ring after warm-up
+    launches0 = shard.stats()["launches"]
+
+    sampler = ClockSampler(local_rank)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        one_step()
+    ev1.record()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    phases = shard.phase_ms()
+    stats = shard.stats()
+    launches = stats["launches"] - launches0 + (args.steps if world > 1 else 0)
+
+    ms_per_step = ms_total / max(args.steps, 1)
+    value = N * args.steps / (ms_total * 1e-3)
+
+    # ---- size-independent checks at the full size (cheap): counts sum to N, labels idempotent ----
+    part = shard.partials.clone()
+    counts_sum = float(part[K * D:K * D + K].sum().item())
+    checks = {"counts_sum_equals_N": bool(counts_sum == N)}
+
+    # ---- roofline of the dominant kernel (the assignment kernel) ----
+    peaks = measured_peaks()
+    t_assign = phases["assign"] * 1e-3
+    flops = 2.0 * n_local * K * D
+    bytes_alg = 4.0 * n_local * D
+    t_tensor, t_hbm = flops / (peaks["tflops"] * 1e12), bytes_alg / (peaks["hbm_gbs"] * 1e9)
+    if t_tensor >= t_hbm:
+        roofline = {"bound": "tensor", "achieved": flops / t_assign / 1e12 if t_assign > 0 else None,
+                    "peak": peaks["tflops"], "unit": "TFLOP/s"}
+    else:
+        roofline = {"bound": "hbm", "achieved": bytes_alg / t_assign / 1e9 if t_assign > 0 else None,
+                    "peak": peaks["hbm_gbs"], "unit": "GB/s"}
+    roofline["frac"] = (roofline["achieved"] / roofline["peak"]) if roofline["achieved"] else None
+    roofline["traffic"] = None          # dram bytes per launch come from the ncu capture under profiles/
+    roofline["peak_source"] = peaks["source"] + (" bf16 dense, sustained" if roofline["bound"] == "tensor" else " copy bandwidth")
+    roofline["kernel"] = {"tc": "tc_assign_kernel", "small": "small_kernel", "simt": "simt_assign_kernel"}[stats["path"]]
+    roofline["kernel_ms"] = phases["assign"]
+    roofline["phase_ms"] = {k: round(v, 4) for k, v in phases.items() if k != "calls"}
+    # whole-iteration roofline of BASELINE.json: slower of 2NKD at peak and 4ND at HBM bandwidth
+    roofline["step_frac"] = max(t_tensor, t_hbm) / (ms_per_step * 1e-3)
+
+    result = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.config), "N": N, "D": D, "K": K, "rows_per_gpu": n_local,
+                   "kernel_path": stats["path"], "seed": SEED, "parallelism": f"rows sharded over {world} GPU(s)",
+                   "l2": "inputs (%.1f GB per GPU) exceed the 126 MB L2; no flush needed" % (n_local * D * 4 / 1e9)
+                   if n_local * D * 4 > 4 * 126e6 else "inputs fit in L2: numbers are L2-resident",
+                   "refined_rows_last_step": stats["ambiguous"], "checks": checks},
+        "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
+    }
+    if args.rows:
+        result["config"]["INVALID"] = "--rows override: not the BASELINE.json configuration"
+
+    # ---- end to end through the public entry point, host buffers, copies inside the timed region ----
+    if not args.no_e2e and world == 1:
+        host, note = pinned_host_copy(X, N, D, K, dev)
+        shard.close()
+        del shard, X, part
+        torch.cuda.empty_cache()
+        result["e2e"] = run_e2e(pkg, host, note, C0, D, K, args.steps, dev)
+        del host
+    elif world > 1:
+        result["e2e"] = None
+
+    # ---- CPU baseline: the oracle port on the host cores, bounded sample (rank 0, N = 1 only) ----
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sample = int(min(N, max(4096, 8e10 / (2.0 * K * D))))
+        step, rows, form = cpu_reference_step_factory(D, K, kind, sample)
+        step()
+        t0 = time.perf_counter()
+        iters = 3
+        for _ in range(iters):
+            step()
+        dt = time.perf_counter() - t0
+        result["cpu_baseline"] = {
+            "value": rows * iters / dt, "unit": UNIT, "cores": host_cores(), "kind": "port",
+            "sample": f"{rows} rows of the same workload (D={D}, K={K}), float64 {form}-form oracle, {iters} iterations",
+        }
+    if rank == 0:
+        print(json.dumps(result))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def pinned_host_copy(X_dev, N, D, K, dev):
+    """The synthetic points copied to pinned host memory (untimed set-up of the e2e leg)."""
+    import psutil
+    import torch
+
+    need = N * D * 4
+    avail = psutil.virtual_memory().available
+    rows, note = N, None
+    if avail < need * 1.3 + (8 << 30):
+        rows = int(max(K, min(N, (avail - (8 << 30)) / 1.3 // (D * 4))))
+        note = f"host RAM available {avail / 1e9:.0f} GB < needed: e2e uses the first {rows} rows"
+    host = torch.empty((rows, D), dtype=torch.float32, pin_memory=True)
+    host.copy_(X_dev[:rows])
+    torch.cuda.synchronize(dev)
+    return host, note
+
+
+def run_e2e(pkg, host, note, C0, D, K, steps, dev):
+    """The same metric through the reference-facing entry point `distribuited_k_means`, points in
+    pinned HOST memory: the timed region holds the pinned H2D staging of every row, the one-time
+    split of the points, `steps` Lloyd iterations, and the D2H of the centroids and of the labels
+    (the reference's `cluster_idx`).  Bytes are per job divided by `steps`."""
+    rows = host.shape[0]
+    t0 = time.perf_counter()
+    res = pkg.distribuited_k_means(host, K, [f"/device:GPU:{dev.index}"], C0, steps)
+    dt = time.perf_counter() - t0
+    out = {
+        "value": rows * res["n_iter"] / dt, "unit": UNIT,
+        "h2d_bytes_per_step": int(rows * D * 4 / max(steps, 1)),
+        "d2h_bytes_per_step": int((K * D * 4 + rows * 4) / max(steps, 1)),
+        "rows": rows, "iterations": res["n_iter"], "seconds": dt,
+        "initialization_time": res["initialization_time"], "computation_time": res["computation_time"],
+        "inertia": res["inertia"],
+    }
+    if note:
+        out["note"] = note
+    return out
+
+
+if __name__ == "__main__":
+    main()

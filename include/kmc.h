@@ -1,0 +1,185 @@
+/*
+ * kmc.h -- C ABI of libkmc_b200.so: the data-parallel K-Means Lloyd iteration of
+ * Jhonsonzhangxing/tensorflow-distributed-clustering, hand-written for NVIDIA B200 (sm_100a).
+ *
+ * The reference has no FFI / op-registration layer: its boundary is the Python function
+ * `distribuited_k_means` (reference scripts/distribuitedClustering.py:180-294).  This header is
+ * the boundary that a Python (ctypes), C or C++ host binds instead of building that TensorFlow
+ * graph.  Each entry point cites the reference lines whose work it replaces.
+ *
+ * Conventions
+ *   - One `kmc_ctx` drives ONE shard of rows on ONE GPU (one process per GPU, or one ctx per
+ *     device inside a single process).  Cross-GPU reduction of the partial buffer is the host's
+ *     job (NCCL all-reduce of `kmc_partials_len` doubles) between kmc_accumulate and kmc_update.
+ *   - All pointers named `dev_*` are device pointers valid on the ctx's device; `host_*` are
+ *     host pointers.  `stream` is a `cudaStream_t` passed as `void*` (NULL = default stream).
+ *     Every call is asynchronous on `stream` unless it returns values to the host.
+ *   - The library allocates no large device memory: the caller provides one workspace
+ *     (`kmc_workspace_bytes` / `kmc_bind_workspace`) and the points buffer, and keeps both alive
+ *     until `kmc_destroy`.
+ *   - Return value: 0 = OK; > 0 = a cudaError_t; < 0 = a library error (KMC_E_*).  A
+ *     human-readable message for the last failure on the calling thread is in kmc_last_error().
+ *   - There is no CPU fallback: every entry point runs CUDA kernels or fails.
+ */
+#ifndef KMC_B200_H_
+#define KMC_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct kmc_ctx kmc_ctx;
+
+/* library error codes (negative) */
+#define KMC_E_INVALID   (-1)   /* bad argument / shape */
+#define KMC_E_STATE     (-2)   /* call order (workspace / points / centroids not bound yet) */
+#define KMC_E_NOMEM     (-3)   /* workspace too small */
+#define KMC_E_UNSUPPORTED (-4) /* requested kernel path cannot run this shape */
+#define KMC_E_DEVICE    (-5)   /* device is not an sm_100 GPU / driver entry point missing */
+
+/* kmc_create flags */
+#define KMC_EMPTY_KEEP      0x0u  /* globally empty cluster keeps its previous centroid (default) */
+#define KMC_EMPTY_NAN       0x1u  /* ... becomes NaN, as the reference's 0/0 at :261 */
+#define KMC_PATH_AUTO       0x00u /* pick the kernel path from (K, D) */
+#define KMC_PATH_SMALL      0x10u /* fused FFMA assign+accumulate, centroids in shared memory */
+#define KMC_PATH_SIMT       0x20u /* exact fp32 register-tiled assign + sorted accumulate */
+#define KMC_PATH_TC         0x30u /* tcgen05/TMEM/TMA split-fp16 assign + exact refine + sorted accumulate */
+#define KMC_PATH_MASK       0xF0u
+
+/* kmc_stage_points source dtypes */
+#define KMC_DTYPE_F32 0
+#define KMC_DTYPE_F64 1
+
+/* index of values returned by kmc_read_stats */
+#define KMC_STAT_INERTIA     0  /* sum_i min_k |x_i - c_k|^2 of the last accumulate (this shard) */
+#define KMC_STAT_SHIFT2      1  /* sum_k |c_new - c_old|^2 of the last update */
+#define KMC_STAT_AMBIGUOUS   2  /* rows the tensor path sent to the exact refine kernel, last pass */
+#define KMC_STAT_KERNEL_PATH 3  /* KMC_PATH_* actually used */
+#define KMC_STAT_LAUNCHES    4  /* kernels launched by this ctx since creation */
+#define KMC_STAT_COUNT       8
+
+/* Version of this ABI (major*1000 + minor). */
+int kmc_version(void);
+
+/* Message describing the last error on the calling thread ("" if none). */
+const char* kmc_last_error(void);
+
+/*
+ * Create the context for one shard: `n_rows` points of dimension `D`, `K` clusters, on CUDA
+ * device `device`.  Replaces the per-GPU graph construction of reference :201-251
+ * (`with tf.device(GPU_name)` ... ) -- here nothing is traced; the call only picks the kernel
+ * path and lays out the workspace.
+ */
+int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, uint32_t flags);
+
+/* Free everything the library owns (streams/events/pinned staging).  The workspace and the
+ * points stay the caller's.  Reference: end of the `with tf.Session` block, :271-282. */
+void kmc_destroy(kmc_ctx* ctx);
+
+/* Bytes of device workspace this ctx needs (labels, sort permutation, partial sums, split
+ * fp16 planes of the points for the tensor path, ...). */
+int64_t kmc_workspace_bytes(const kmc_ctx* ctx);
+
+/* Hand the workspace to the ctx (256-byte aligned device pointer). */
+int kmc_bind_workspace(kmc_ctx* ctx, void* dev_workspace, int64_t bytes);
+
+/*
+ * Bind the shard's points: row-major fp32 [n_rows, D], resident on the device for all
+ * iterations.  Replaces `X = tf.Variable(X_mat)` (:217) + the initializer run (:273).  On the
+ * tensor path this also launches the one-time split of the points into the scaled fp16
+ * hi/lo planes the tcgen05 kernel reads.
+ */
+int kmc_bind_points(kmc_ctx* ctx, const float* dev_points, void* stream);
+
+/*
+ * Pinned, double-buffered host->device staging of rows [row0, row0+n_rows) of a host array
+ * (fp32 or fp64, row-major [*, D]) into `dev_dst` (fp32 [n_rows, D]); fp64 is converted on the
+ * device.  Replaces the feed of `all_data` + `tf.split` + per-GPU variable init (:196-197, :217,
+ * :273).  `dev_dst` is any fp32 device buffer (normally a slice of the points buffer).
+ * Returns after the last chunk has been queued and the host buffer may be reused.
+ */
+int kmc_stage_points(kmc_ctx* ctx, float* dev_dst, const void* host_src, int src_dtype,
+                     int64_t row0, int64_t n_rows, void* stream);
+
+/* Set / read the K x D fp32 centroids (host, row-major).  Replaces `global_centroids =
+ * tf.Variable(initial_centers)` (:199) and the fetch of `global_centroids` (:279). */
+int kmc_set_centroids(kmc_ctx* ctx, const float* host_centroids, void* stream);
+int kmc_get_centroids(kmc_ctx* ctx, float* host_centroids, void* stream);
+
+/* Device address of the centroids (fp32 [K, D]) inside the workspace, for hosts that want to
+ * broadcast or inspect them without a host round trip. */
+float* kmc_centroids_ptr(kmc_ctx* ctx);
+
+/*
+ * One assignment + accumulation pass over the shard against the current centroids: nearest
+ * centroid per row (lowest index on ties), per-cluster sums, counts and the inertia.
+ * Replaces the distance / argmin sub-graph (:221-234), the K per-cluster gather+mean ops
+ * (:237-242), the CPU bincount (:244-246) and the mean*count reconstruction (:248).
+ * The N x K distance matrix is never formed.  Result: the partial buffer
+ *   double[K*D] sums (row-major) | double[K] counts | double[1] inertia | double[1] reserved
+ * at kmc_partials_ptr(); it is overwritten by every call.
+ */
+int kmc_accumulate(kmc_ctx* ctx, void* stream);
+double* kmc_partials_ptr(kmc_ctx* ctx);
+int64_t kmc_partials_len(const kmc_ctx* ctx);   /* = K*D + K + 2 */
+
+/*
+ * Centroid update from the (all-reduced) partial buffer: c[k] = sums[k] / counts[k], the squared
+ * centre shift, and on the tensor path the next iteration's split centroid planes and norms.
+ * Replaces add_n / tile / div / transpose / assign on /cpu:0 (:257-263).
+ */
+int kmc_update(kmc_ctx* ctx, void* stream);
+
+/*
+ * Single-GPU Lloyd loop: up to `max_iters` x (kmc_accumulate, kmc_update) on `stream`, stopping
+ * early when shift2 <= tol (tol <= 0: never, the reference's behaviour).  Replaces the
+ * `for i in range(n_max_iters): sess.run(...)` loop (:277-280).  Synchronises the stream before
+ * returning.  Outputs (any may be NULL): iterations done, inertia of the last accumulate,
+ * shift2 of the last update.
+ */
+int kmc_iterate(kmc_ctx* ctx, int max_iters, double tol, int* n_iter_out,
+                double* inertia_out, double* shift2_out, void* stream);
+
+/*
+ * Label-only pass against the current centroids: dev_labels[i] = argmin_k |x_i - c_k|^2
+ * (int32, n_rows entries).  Replaces the second `sess.run(result_matrix, ...)` that ships the
+ * whole N x K matrix to the CPU for an argmin (:235, :255, :282).
+ */
+int kmc_assign(kmc_ctx* ctx, int32_t* dev_labels, void* stream);
+
+/* Synchronise `stream` and copy KMC_STAT_COUNT doubles (see KMC_STAT_*) to the host. */
+int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
+
+/* Tunable parameters (advanced; defaults are chosen at kmc_create). */
+#define KMC_PARAM_TC_GAMMA  1   /* relative error bound of the split-fp16 tensor scores used to
+                                   decide which rows go to the exact refine kernel */
+#define KMC_PARAM_PROFILE   2   /* non-zero: record CUDA events around each phase (see below) */
+int kmc_set_param(kmc_ctx* ctx, int param, double value);
+
+/*
+ * Device time per phase, averaged over the kmc_accumulate / kmc_update calls made since the last
+ * call of this function (at most the 32 most recent), in milliseconds, measured with CUDA events
+ * on the stream the kernels were launched on (needs KMC_PARAM_PROFILE).  Synchronises the events.
+ *   out_ms[0] assignment kernel (fused small kernel / SIMT assign / tcgen05 assign)
+ *   out_ms[1] exact refine of ambiguous rows (tensor path)      out_ms[2] sorted accumulation
+ *   out_ms[3] centroid update (+ centroid plane preparation)    out_ms[4] calls averaged
+ * Replaces the reference's external nvprof log parsing (scripts/compileResults.py:58-137) for
+ * the phases of this path.
+ */
+#define KMC_PHASE_COUNT 5
+int kmc_get_phase_ms(kmc_ctx* ctx, float* out_ms, int n);
+
+/*
+ * Debug / test hook of the tensor path: the raw approximate scores
+ * s[i,k] = |c_k|^2 - 2 x_i . c_k (fp32, [n_rows, K] row-major) as the tcgen05 kernel sees them
+ * before the argmin.  Only for small shards (n_rows * K * 4 bytes of caller memory).
+ * No counterpart in the reference (which materialises the full distance matrix at :230).
+ */
+int kmc_debug_tc_scores(kmc_ctx* ctx, float* dev_scores, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KMC_B200_H_ */

@@ -1,0 +1,364 @@
+"""Host side of the B200 K-Means Lloyd path: thin Python over the C ABI of libkmc_b200.so.
+
+Mirrors the reference's entry point ``distribuited_k_means`` and its caller ``run_experiments``
+(reference scripts/distribuitedClustering.py:180-294 and :296-318): same names, positional forms,
+result-dictionary keys and timer meanings.  PyTorch is used only for device memory, streams and
+the cross-GPU all-reduce; every arithmetic step runs in hand-written sm_100a kernels behind
+``include/kmc.h``.  There is no CPU or PyTorch fallback: without the built library or without a
+B200 these functions raise.
+"""
+from __future__ import annotations
+
+import ctypes
+import time
+from ctypes import byref, c_double, c_int, c_void_p
+
+import numpy as np
+
+from . import _lib as L
+from .datagen import kmeanspp_init
+from .sharding import parse_gpu_names, shard_ranges
+
+
+def _torch():
+    import torch
+    return torch
+
+
+class LloydShard:
+    """One contiguous shard of rows resident on one GPU, driven through one ``kmc_ctx``.
+
+    The reference's per-GPU scope (``with tf.device(GPU_name)``, :201-251) holds the same state:
+    the shard ``X = tf.Variable(X_mat)`` and the ops that produce its partial sums and counts.
+    """
+
+    def __init__(self, n_rows: int, D: int, K: int, device, empty: str = "keep", path: str = "auto"):
+        torch = _torch()
+        self.lib = L.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError("libkmc_b200 needs a CUDA device (sm_100a); no CPU fallback exists")
+        self.device = torch.device(device)
+        self.n, self.D, self.K = int(n_rows), int(D), int(K)
+        flags = L.PATH_FLAGS[path] | (L.KMC_EMPTY_NAN if empty == "nan" else L.KMC_EMPTY_KEEP)
+        if empty not in ("keep", "nan"):
+            raise ValueError("empty must be 'keep' or 'nan'")
+        self._ctx = c_void_p()
+        L.check(self.lib.kmc_create(byref(self._ctx), self.device.index or 0, self.n, self.D, self.K, flags))
+        nbytes = int(self.lib.kmc_workspace_bytes(self._ctx))
+        with torch.cuda.device(self.device):
+            self.workspace = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=self.device)
+            L.check(self.lib.kmc_bind_workspace(self._ctx, c_void_p(self.workspace.data_ptr()), nbytes))
+        self.points = None
+        plen = int(self.lib.kmc_partials_len(self._ctx))
+        off = int(self.lib.kmc_partials_ptr(self._ctx)) - self.workspace.data_ptr()
+        # [K*D sums | K counts | inertia | reserved] as float64, living inside the workspace
+        self.partials = self.workspace[off:off + plen * 8].view(torch.float64)
+        coff = int(self.lib.kmc_centroids_ptr(self._ctx)) - self.workspace.data_ptr()
+        self.centroids_dev = self.workspace[coff:coff + self.K * self.D * 4].view(torch.float32).view(self.K, self.D)
+
+    # -- lifetime -------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            self.lib.kmc_destroy(self._ctx)
+            self._ctx = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return c_void_p(_torch().cuda.current_stream(self.device).cuda_stream)
+
+    # -- data -----------------------------------------------------------------------------------
+    def bind_points(self, points):
+        """Borrow a float32 CUDA tensor [n_rows, D] (kept alive by this object)."""
+        torch = _torch()
+        if points.device != self.device or points.dtype != torch.float32 or not points.is_contiguous():
+            raise ValueError("points must be a contiguous float32 tensor on the shard's device")
+        if tuple(points.shape) != (self.n, self.D):
+            raise ValueError(f"points shape {tuple(points.shape)} != {(self.n, self.D)}")
+        self.points = points
+        with torch.cuda.device(self.device):
+            L.check(self.lib.kmc_bind_points(self._ctx, c_void_p(points.data_ptr()), self._stream()))
+
+    def stage_from_host(self, host, row0: int, batch_size=None):
+        """Pinned, chunked H2D of rows [row0, row0 + n_rows) of a host array, then bind them.
+
+        Replaces feeding ``all_data`` and the per-GPU variable initialisation (:196-197, :217, :273).
+        ``host`` is a C-contiguous float32/float64 NumPy array or CPU tensor of shape [N, D].
+        """
+        torch = _torch()
+        if isinstance(host, torch.Tensor):
+            arr_ptr, dt = host.data_ptr(), host.dtype
+            is64 = dt == torch.float64
+            if dt not in (torch.float32, torch.float64) or not host.is_contiguous():
+                raise ValueError("host tensor must be contiguous float32/float64")
+        else:
+            if host.dtype not in (np.float32, np.float64) or not host.flags.c_contiguous:
+                raise ValueError("host array must be C-contiguous float32/float64")
+            arr_ptr, is64 = host.ctypes.data, host.dtype == np.float64
+        with torch.cuda.device(self.device):
+            pts = torch.empty((self.n, self.D), dtype=torch.float32, device=self.device)
+            step = self.n if not batch_size else max(1, int(batch_size))
+            for r in range(0, self.n, max(step, 1)):
+                nr = min(step, self.n - r)
+                dst = c_void_p(pts.data_ptr() + r * self.D * 4)
+                L.check(self.lib.kmc_stage_points(self._ctx, dst, c_void_p(arr_ptr),
+                                                  L.KMC_DTYPE_F64 if is64 else L.KMC_DTYPE_F32,
+                                                  row0 + r, nr, self._stream()))
+        self.bind_points(pts)
+
+    def set_centroids(self, C):
+        C = np.ascontiguousarray(np.asarray(C, dtype=np.float32))
+        if C.shape != (self.K, self.D):
+            raise ValueError(f"initial centres shape {C.shape} != {(self.K, self.D)}")
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_set_centroids(self._ctx, c_void_p(C.ctypes.data), self._stream()))
+
+    def get_centroids(self) -> np.ndarray:
+        out = np.empty((self.K, self.D), dtype=np.float32)
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_get_centroids(self._ctx, c_void_p(out.ctypes.data), self._stream()))
+        return out
+
+    # -- iteration ------------------------------------------------------------------------------
+    def accumulate(self):
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_accumulate(self._ctx, self._stream()))
+
+    def update(self):
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_update(self._ctx, self._stream()))
+
+    def iterate(self, max_iters: int, tol: float = 0.0):
+        n_iter, inertia, shift2 = c_int(0), c_double(0.0), c_double(0.0)
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_iterate(self._ctx, int(max_iters), float(tol), byref(n_iter), byref(inertia),
+                                         byref(shift2), self._stream()))
+        return n_iter.value, inertia.value, shift2.value
+
+    def assign(self, out=None):
+        torch = _torch()
+        with torch.cuda.device(self.device):
+            if out is None:
+                out = torch.empty(self.n, dtype=torch.int32, device=self.device)
+            L.check(self.lib.kmc_assign(self._ctx, c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def stats(self) -> dict:
+        buf = (c_double * L.KMC_STAT_COUNT)()
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_read_stats(self._ctx, buf, self._stream()))
+        return {
+            "inertia": buf[L.KMC_STAT_INERTIA], "shift2": buf[L.KMC_STAT_SHIFT2],
+            "ambiguous": int(buf[L.KMC_STAT_AMBIGUOUS]),
+            "path": L.PATH_NAMES.get(int(buf[L.KMC_STAT_KERNEL_PATH]), "?"),
+            "launches": int(buf[L.KMC_STAT_LAUNCHES]),
+        }
+
+    def set_param(self, param: int, value: float):
+        L.check(self.lib.kmc_set_param(self._ctx, int(param), float(value)))
+
+    def enable_profile(self, on: bool = True):
+        self.set_param(L.KMC_PARAM_PROFILE, 1.0 if on else 0.0)
+
+    def phase_ms(self) -> dict:
+        """Average device milliseconds per phase since the last call (needs enable_profile)."""
+        from ctypes import c_float
+        buf = (c_float * L.KMC_PHASE_COUNT)()
+        L.check(self.lib.kmc_get_phase_ms(self._ctx, buf, L.KMC_PHASE_COUNT))
+        return {"assign": buf[0], "refine": buf[1], "accumulate": buf[2], "update": buf[3], "calls": int(buf[4])}
+
+    def debug_tc_scores(self):
+        torch = _torch()
+        with torch.cuda.device(self.device):
+            out = torch.empty((self.n, self.K), dtype=torch.float32, device=self.device)
+            L.check(self.lib.kmc_debug_tc_scores(self._ctx, c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+
+# ---------------------------------------------------------------------------------------------
+# Cross-shard reduction (the reference's add_n on /cpu:0, :257-258)
+# ---------------------------------------------------------------------------------------------
+def allreduce_partials_single_process(shards):
+    """Sum the partial buffers of several shards driven by ONE process (one ctx per GPU)."""
+    if len(shards) == 1:
+        return
+    torch = _torch()
+    torch.cuda.nccl.all_reduce([s.partials for s in shards])
+
+
+def lloyd_loop(shards, n_max_iters: int, tol: float = 0.0, reduce_fn=None):
+    """Iterate ``n_max_iters`` times (reference :277-280): accumulate on every shard, sum the
+    partial buffers across shards, update on every shard (identical arithmetic on identical
+    inputs keeps the replicated centroids bit-identical, so no broadcast is needed).
+
+    ``shards`` is a list of shard engines in this process (objects with ``accumulate()``,
+    ``update()``, ``partials`` and ``stats()``); ``reduce_fn(shards)`` sums their ``partials`` in
+    place -- across the list, and across processes when every rank runs this loop on its own
+    shard (``reduce_fn = lambda s: torch.distributed.all_reduce(s[0].partials)``).
+    ``tol > 0`` stops when the squared centre shift drops to ``tol`` (same decision on every
+    rank: the shift is computed from the reduced buffer).  Returns (iterations, inertia, shift2).
+    """
+    if reduce_fn is None:
+        reduce_fn = allreduce_partials_single_process
+    n_iter, inertia, shift2 = 0, float("nan"), float("nan")
+    for _ in range(int(n_max_iters)):
+        for s in shards:
+            s.accumulate()
+        reduce_fn(shards)
+        for s in shards:
+            s.update()
+        n_iter += 1
+        if tol > 0.0:
+            st = shards[0].stats()
+            inertia, shift2 = st["inertia"], st["shift2"]
+            if shift2 <= tol:
+                break
+    if shards:
+        st = shards[0].stats()
+        inertia, shift2 = st["inertia"], st["shift2"]
+    return n_iter, inertia, shift2
+
+
+# ---------------------------------------------------------------------------------------------
+# Drop-in entry points
+# ---------------------------------------------------------------------------------------------
+def _as_host_matrix(data_batch):
+    torch = _torch()
+    if isinstance(data_batch, torch.Tensor):
+        if data_batch.dim() != 2:
+            raise ValueError("data_batch must be [N, D]")
+        return data_batch
+    arr = np.asarray(data_batch)
+    if arr.ndim != 2:
+        raise ValueError("data_batch must be [N, D]")
+    if arr.dtype not in (np.float32, np.float64):
+        arr = arr.astype(np.float64)
+    return np.ascontiguousarray(arr)
+
+
+def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_iters=20, *,
+                         seed=None, batch_size=None, tol=0.0, empty="keep", path="auto",
+                         return_labels=True):
+    """Data-parallel K-Means (Lloyd) on one or more B200s -- drop-in for the reference function.
+
+    Accepts both reference call shapes: ``(data_batch, K, GPU_names, initial_centers,
+    n_max_iters)`` (how ``run_experiments`` calls it, :303) and HEAD's ``(data_batch, K,
+    GPU_names, n_max_iters)`` (:180), where the centres come from k-means++ (:191; seeded here by
+    ``seed``).  ``GPU_names`` is a list of device names as returned by the reference's
+    ``get_available_gpus()`` (or an int = number of GPUs).  ``batch_size`` = rows per pinned H2D
+    staging chunk; ``tol`` = optional early stop on the squared centre shift (0 = run all
+    ``n_max_iters`` like the reference).
+
+    Returns the reference's result dictionary (:284-292): ``end_center``, ``cluster_idx``,
+    ``centroids`` (labels of the last GPU's shard), ``init_center``, ``setup_time``,
+    ``initialization_time``, ``computation_time``, ``n_iter`` -- plus ``inertia``, ``center_shift``,
+    ``converged``.
+    """
+    torch = _torch()
+    setup_ts = time.time()
+    if initial_centers is not None and np.isscalar(initial_centers) and not isinstance(initial_centers, bool):
+        # HEAD's 4-positional form: the 4th argument is n_max_iters (:180)
+        n_max_iters, initial_centers = int(initial_centers), None
+    K = int(K)
+    n_max_iters = int(n_max_iters)
+    if K <= 0 or n_max_iters < 0:
+        raise ValueError("K must be positive and n_max_iters non-negative")
+    data = _as_host_matrix(data_batch)
+    N, D = int(data.shape[0]), int(data.shape[1])
+    if K > N:
+        raise ValueError(f"K={K} clusters but only N={N} points")
+    n_avail = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n_avail == 0:
+        raise RuntimeError("no CUDA device: the B200 K-Means path has no CPU fallback")
+    dev_ids = parse_gpu_names(GPU_names, n_avail)
+    ranges = shard_ranges(N, len(dev_ids))                                    # :184
+    on_device = isinstance(data, torch.Tensor) and data.is_cuda
+
+    if initial_centers is None:                                               # :191
+        host_view = data.detach().cpu().numpy() if isinstance(data, torch.Tensor) else data
+        initial_centers = kmeanspp_init(host_view, K, seed)
+    init_center = np.array(initial_centers, dtype=np.float32, copy=True)
+    if init_center.shape != (K, D):
+        raise ValueError(f"initial_centers shape {init_center.shape} != {(K, D)}")
+
+    shards = [LloydShard(r1 - r0, D, K, torch.device("cuda", dev), empty=empty, path=path)
+              for dev, (r0, r1) in zip(dev_ids, ranges)]
+    setup_time = float(time.time() - setup_ts)
+
+    # ---- initialisation: H2D of every shard + centroids (:272-274) ----
+    initialization_ts = time.time()
+    for s, (r0, r1) in zip(shards, ranges):
+        if on_device:
+            blk = data[r0:r1]
+            if blk.device != s.device or blk.dtype != torch.float32 or not blk.is_contiguous():
+                blk = blk.to(device=s.device, dtype=torch.float32).contiguous()
+            s.bind_points(blk)
+        else:
+            s.stage_from_host(data, r0, batch_size)
+        s.set_centroids(init_center)
+    for s in shards:
+        torch.cuda.synchronize(s.device)
+    initialization_time = float(time.time() - initialization_ts)
+
+    # ---- the Lloyd loop (:277-280) ----
+    aux_ts = time.time()
+    if len(shards) == 1:
+        n_iter, inertia, shift2 = shards[0].iterate(n_max_iters, tol)
+    else:
+        n_iter, inertia, shift2 = lloyd_loop(shards, n_max_iters, tol)
+    for s in shards:
+        torch.cuda.synchronize(s.device)
+    computation_time = float(time.time() - aux_ts)
+
+    # ---- label pass against the updated centroids (:255, :282) ----
+    end_center = shards[0].get_centroids()
+    cluster_idx = None
+    last_labels = None
+    if return_labels:
+        parts = [s.assign() for s in shards]
+        for s in shards:
+            torch.cuda.synchronize(s.device)
+        host_parts = [p.cpu().numpy().astype(np.int64) for p in parts]
+        cluster_idx = np.concatenate(host_parts) if host_parts else np.empty(0, np.int64)
+        last_labels = host_parts[-1]
+    for s in shards:
+        s.close()
+
+    return {
+        "end_center": end_center,
+        "cluster_idx": cluster_idx,
+        "centroids": last_labels,
+        "init_center": init_center,
+        "setup_time": setup_time,
+        "initialization_time": initialization_time,
+        "computation_time": computation_time,
+        "n_iter": n_iter,
+        "inertia": inertia,
+        "center_shift": float(np.sqrt(shift2)) if shift2 == shift2 else float("nan"),
+        "converged": bool(tol > 0.0 and shift2 <= tol),
+    }
+
+
+def run_experiments(batches, GPU_names, K, initial_centers, n_max_iters, func=None, **kwargs):
+    """The reference's batch driver (:296-318): run ``func`` per batch, average the end centres
+    across batches (``np.mean(result, axis=0)``, :310) and add up the three timers."""
+    func = func or distribuited_k_means
+    result, setup_time, initialization_time, computation_time = [], 0.0, 0.0, 0.0
+    for batch in batches:
+        batch_run = func(batch, K, GPU_names, initial_centers, n_max_iters, **kwargs)
+        result.append(batch_run["end_center"])
+        setup_time += batch_run["setup_time"]
+        initialization_time += batch_run["initialization_time"]
+        computation_time += batch_run["computation_time"]
+    return {
+        "end_center": np.mean(result, axis=0),
+        "init_center": initial_centers,
+        "setup_time": setup_time,
+        "initialization_time": initialization_time,
+        "computation_time": computation_time,
+        "n_iter": n_max_iters,
+    }

@@ -1,0 +1,307 @@
+// Per-cluster sums, counts and inertia for large K*D, where per-CTA private accumulators do not
+// fit on chip and a scatter-add of N*D values through atomics would be ~10x slower than HBM.
+// Instead the labels are counting-sorted into a row permutation (rows of one cluster become a
+// contiguous run) and each run is summed with plain coalesced row loads:
+//     histogram -> exclusive scan -> scatter (perm) -> segmented row sum (+ exact inertia)
+// One extra streaming pass over the fp32 points, no atomics on the data path; fp32 partial sums
+// over <= 128 rows per lane, fp64 from the CTA level upward.
+//
+// Replaces reference scripts/distribuitedClustering.py:237-242 (K x equal/where/gather/reduce_mean),
+// :244-246 (D2H of the labels + CPU bincount) and :248 (mean*count = sum).  Sums are formed
+// directly, so a cluster that is empty on this shard contributes 0, not the reference's NaN.
+#include "kmc_common.cuh"
+#include "kmc_device.cuh"
+
+namespace kmc {
+
+constexpr int kSegRows = 1024;        // rows of one cluster summed by one CTA
+constexpr int kScatterChunk = 16384;  // rows per CTA in the scatter pass
+constexpr int kSegPMax = 4;           // column passes per lane
+
+// ---- histogram --------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) hist_kernel(const int32_t* __restrict__ labels, int64_t n, int K,
+                                                   unsigned int* __restrict__ hist, int use_smem) {
+    extern __shared__ unsigned int lh[];
+    if (use_smem) {
+        for (int i = threadIdx.x; i < K; i += blockDim.x) lh[i] = 0;
+        __syncthreads();
+    }
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int l = labels[i];
+        if ((unsigned)l < (unsigned)K) {
+            if (use_smem) atomicAdd(&lh[l], 1u); else atomicAdd(&hist[l], 1u);
+        }
+    }
+    if (use_smem) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < K; i += blockDim.x) {
+            const unsigned int v = lh[i];
+            if (v) atomicAdd(&hist[i], v);
+        }
+    }
+}
+
+// ---- scan: offsets[k] = rows before cluster k; segoff[k] = segments before cluster k ------------
+__global__ void __launch_bounds__(1024) scan_kernel(const unsigned int* __restrict__ hist, int K,
+                                                    unsigned int* __restrict__ offsets,
+                                                    unsigned int* __restrict__ segoff,
+                                                    double* __restrict__ counts_out) {
+    __shared__ unsigned int tot_rows[1024];
+    __shared__ unsigned int tot_segs[1024];
+    const int t = threadIdx.x;
+    const int per = (K + 1023) / 1024;
+    const int b = t * per, e = min(K, b + per);
+    unsigned int r = 0, sgs = 0;
+    for (int i = b; i < e; ++i) {
+        const unsigned int h = hist[i];
+        r += h;
+        sgs += (h + kSegRows - 1) / kSegRows;
+    }
+    tot_rows[t] = r;
+    tot_segs[t] = sgs;
+    __syncthreads();
+    // Hillis-Steele inclusive scan over the 1024 thread totals
+    for (int o = 1; o < 1024; o <<= 1) {
+        unsigned int a = 0, c2 = 0;
+        if (t >= o) { a = tot_rows[t - o]; c2 = tot_segs[t - o]; }
+        __syncthreads();
+        tot_rows[t] += a;
+        tot_segs[t] += c2;
+        __syncthreads();
+    }
+    unsigned int ro = tot_rows[t] - r, so = tot_segs[t] - sgs;
+    for (int i = b; i < e; ++i) {
+        const unsigned int h = hist[i];
+        offsets[i] = ro;
+        segoff[i] = so;
+        counts_out[i] = (double)h;
+        ro += h;
+        so += (h + kSegRows - 1) / kSegRows;
+    }
+    if (t == 1023) { offsets[K] = tot_rows[1023]; segoff[K] = tot_segs[1023]; }
+}
+
+// ---- scatter: perm[offsets[l] + rank] = row ----------------------------------------------------
+__global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict__ labels, int64_t n, int K,
+                                                      const unsigned int* __restrict__ offsets,
+                                                      unsigned int* __restrict__ cursor,
+                                                      int32_t* __restrict__ perm, int use_smem) {
+    extern __shared__ unsigned int sm[];
+    unsigned int* lcnt = sm;        // [K] local counts, then local cursors
+    unsigned int* lbase = sm + K;   // [K] global position of this CTA's first row of each cluster
+    const int64_t r0 = (int64_t)blockIdx.x * kScatterChunk;
+    const int64_t r1 = min(n, r0 + (int64_t)kScatterChunk);
+    if (!use_smem) {
+        for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
+            const int l = labels[i];
+            if ((unsigned)l < (unsigned)K) perm[offsets[l] + atomicAdd(&cursor[l], 1u)] = (int32_t)i;
+        }
+        return;
+    }
+    for (int i = threadIdx.x; i < K; i += blockDim.x) lcnt[i] = 0;
+    __syncthreads();
+    for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
+        const int l = labels[i];
+        if ((unsigned)l < (unsigned)K) atomicAdd(&lcnt[l], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < K; i += blockDim.x) {
+        const unsigned int cnt = lcnt[i];
+        if (cnt) lbase[i] = offsets[i] + atomicAdd(&cursor[i], cnt);
+        lcnt[i] = 0;
+    }
+    __syncthreads();
+    for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
+        const int l = labels[i];
+        if ((unsigned)l < (unsigned)K) perm[lbase[l] + atomicAdd(&lcnt[l], 1u)] = (int32_t)i;
+    }
+}
+
+// ---- segmented row sum ---------------------------------------------------------------------------
+template <int VEC> struct RowVec;
+template <> struct RowVec<4> {
+    float v[4];
+    __device__ __forceinline__ void load(const float* p) {
+        const float4 t = ld_stream_f4(reinterpret_cast<const float4*>(p));
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
+};
+template <> struct RowVec<1> {
+    float v[1];
+    __device__ __forceinline__ void load(const float* p) { v[0] = ld_stream_f1(p); }
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict__ cent,
+              const int32_t* __restrict__ perm, const unsigned int* __restrict__ offsets,
+              const unsigned int* __restrict__ segoff, double* __restrict__ partials, int lpr_log2) {
+    __shared__ float red[8][32 * VEC * kSegPMax];
+    __shared__ double red_in[8];
+    const unsigned int seg_total = segoff[K];
+    const unsigned int b = blockIdx.x;
+    if (b >= seg_total) return;
+    // cluster of this segment: largest k with segoff[k] <= b
+    int lo = 0, hi = K - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (segoff[mid] <= b) lo = mid; else hi = mid - 1;
+    }
+    const int k = lo;
+    const unsigned int seg = b - segoff[k];
+    const unsigned int row_b = offsets[k] + seg * kSegRows;
+    const unsigned int row_e = min(offsets[k + 1], row_b + (unsigned)kSegRows);
+    const int nrows = (int)(row_e - row_b);
+
+    const int LPR = 1 << lpr_log2;             // lanes cooperating on one row
+    const int RPW = 32 >> lpr_log2;            // rows per warp step
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cl = lane & (LPR - 1), sub = lane >> lpr_log2;
+    const int col0 = blockIdx.y * (LPR * VEC * kSegPMax);
+
+    float acc[kSegPMax][VEC], cen[kSegPMax][VEC];
+    bool on[kSegPMax];
+#pragma unroll
+    for (int p = 0; p < kSegPMax; ++p) {
+        const int col = col0 + (p * LPR + cl) * VEC;
+        on[p] = col < D;
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+            acc[p][e] = 0.f;
+            cen[p][e] = on[p] ? cent[(int64_t)k * D + col + e] : 0.f;
+        }
+    }
+    float inert = 0.f;
+    const int step = 8 * RPW;
+    int r = warp * RPW + sub;
+    // two rows in flight per lane
+    for (; r + step < nrows; r += 2 * step) {
+        const int64_t i0 = perm[row_b + r], i1 = perm[row_b + r + step];
+        RowVec<VEC> a[kSegPMax], c2[kSegPMax];
+#pragma unroll
+        for (int p = 0; p < kSegPMax; ++p)
+            if (on[p]) {
+                const int col = col0 + (p * LPR + cl) * VEC;
+                a[p].load(x + i0 * D + col);
+                c2[p].load(x + i1 * D + col);
+            }
+#pragma unroll
+        for (int p = 0; p < kSegPMax; ++p)
+            if (on[p]) {
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    acc[p][e] += a[p].v[e];
+                    float t = a[p].v[e] - cen[p][e];
+                    inert = fmaf(t, t, inert);
+                    acc[p][e] += c2[p].v[e];
+                    t = c2[p].v[e] - cen[p][e];
+                    inert = fmaf(t, t, inert);
+                }
+            }
+    }
+    for (; r < nrows; r += step) {
+        const int64_t i0 = perm[row_b + r];
+#pragma unroll
+        for (int p = 0; p < kSegPMax; ++p)
+            if (on[p]) {
+                const int col = col0 + (p * LPR + cl) * VEC;
+                RowVec<VEC> a;
+                a.load(x + i0 * D + col);
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) {
+                    acc[p][e] += a.v[e];
+                    const float t = a.v[e] - cen[p][e];
+                    inert = fmaf(t, t, inert);
+                }
+            }
+    }
+    // fold the RPW row-groups of a warp together
+    for (int o = LPR; o < 32; o <<= 1) {
+#pragma unroll
+        for (int p = 0; p < kSegPMax; ++p)
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) acc[p][e] += __shfl_xor_sync(0xffffffffu, acc[p][e], o);
+    }
+    if (sub == 0) {
+#pragma unroll
+        for (int p = 0; p < kSegPMax; ++p)
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) red[warp][(p * LPR + cl) * VEC + e] = acc[p][e];
+    }
+    const double in_w = warp_sum((double)inert);
+    if (lane == 0) red_in[warp] = in_w;
+    __syncthreads();
+    const int ncols = LPR * VEC * kSegPMax;
+    for (int cidx = threadIdx.x; cidx < ncols; cidx += blockDim.x) {
+        const int col = col0 + cidx;
+        if (col < D) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s += (double)red[w][cidx];
+            atomicAdd(partials + (int64_t)k * D + col, s);
+        }
+    }
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += red_in[w];
+        atomicAdd(partials + (int64_t)K * D + K, s);
+    }
+}
+
+int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s) {
+    const int K = (int)c->K, D = (int)c->D;
+    unsigned int* hist = c->at<unsigned int>(c->off_hist);
+    unsigned int* cursor = c->at<unsigned int>(c->off_cursor);
+    unsigned int* offsets = c->at<unsigned int>(c->off_offsets);
+    unsigned int* segoff = c->at<unsigned int>(c->off_segoff);
+    // hist and cursor are adjacent in the workspace: one memset clears both
+    KMC_CUDA(cudaMemsetAsync(hist, 0, (size_t)(c->off_offsets - c->off_hist), s));
+
+    const int hist_smem_ok = (size_t)K * 4 <= 96 * 1024;
+    {
+        int64_t blocks = (c->n + 256 * 16 - 1) / (256 * 16);
+        const int64_t cap = (int64_t)c->sm_count * 8;
+        blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+        const size_t sm = hist_smem_ok ? (size_t)K * 4 : 0;
+        if (sm > 48 * 1024)
+            KMC_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        hist_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, c->n, K, hist, hist_smem_ok);
+        KMC_CUDA(cudaGetLastError());
+    }
+    scan_kernel<<<1, 1024, 0, s>>>(hist, K, offsets, segoff, c->partials() + (int64_t)K * D);
+    KMC_CUDA(cudaGetLastError());
+    {
+        const int sc_smem_ok = (size_t)K * 8 <= 192 * 1024;
+        const size_t sm = sc_smem_ok ? (size_t)K * 8 : 0;
+        const int64_t blocks = (c->n + kScatterChunk - 1) / kScatterChunk;
+        if (sm > 48 * 1024)
+            KMC_CUDA(cudaFuncSetAttribute(scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        if (blocks > 0) {
+            scatter_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, c->n, K, offsets, cursor, c->perm(), sc_smem_ok);
+            KMC_CUDA(cudaGetLastError());
+        }
+    }
+    {
+        const bool vec4 = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(c->points) & 15) == 0);
+        const int vec = vec4 ? 4 : 1;
+        int lpr_log2 = 0;
+        while ((1 << lpr_log2) < 32 && (1 << lpr_log2) * vec < D) ++lpr_log2;
+        const int cols_per_block = (1 << lpr_log2) * vec * kSegPMax;
+        const unsigned gy = (unsigned)((D + cols_per_block - 1) / cols_per_block);
+        const int64_t gx = (c->n + kSegRows - 1) / kSegRows + K;
+        dim3 grid((unsigned)gx, gy);
+        if (vec4)
+            segsum_kernel<4><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), c->perm(), offsets, segoff,
+                                                  c->partials(), lpr_log2);
+        else
+            segsum_kernel<1><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), c->perm(), offsets, segoff,
+                                                  c->partials(), lpr_log2);
+        KMC_CUDA(cudaGetLastError());
+    }
+    c->launches += 4;
+    return 0;
+}
+
+}  // namespace kmc

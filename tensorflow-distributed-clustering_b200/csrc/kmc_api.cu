@@ -1,0 +1,445 @@
+// C ABI of libkmc_b200 (see include/kmc.h): context, workspace layout, host<->device staging and
+// the per-iteration orchestration of the kernels.  No CPU fallback anywhere: every entry point
+// launches CUDA kernels on an sm_100 device or returns an error.
+#include "kmc_common.cuh"
+#include "kmc_device.cuh"
+
+#include <cstring>
+#include <new>
+#include <string>
+#include <thread>
+#include <vector>
+
+namespace kmc {
+
+static thread_local std::string g_last_error;
+
+void set_error(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+}
+
+static int64_t align256(int64_t v) { return (v + 255) & ~(int64_t)255; }
+
+static void layout_workspace(kmc_ctx* c) {
+    int64_t off = 0;
+    auto take = [&](int64_t bytes) { int64_t o = off; off = align256(off + bytes); return o; };
+    c->off_stats = take(sizeof(DeviceStats));
+    c->off_centroids = take(c->K * c->D * 4);
+    c->off_partials = take((c->K * c->D + c->K + 2) * 8);
+    if (c->path != KMC_PATH_SMALL) {
+        c->off_hist = take(c->K * 4);
+        c->off_cursor = take(c->K * 4);
+        c->off_offsets = take((c->K + 1) * 4);
+        c->off_segoff = take((c->K + 1) * 4);
+        c->off_labels = take(c->n * 4);
+        c->off_perm = take(c->n * 4);
+    }
+    if (c->path == KMC_PATH_TC) {
+        c->off_xnorm = take(c->n * 4);
+        c->off_cnorm = take(c->K_pad * 4);
+        c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
+        c->off_xhi = take(c->n * c->D_pad * 2);
+        c->off_xlo = take(c->n * c->D_pad * 2);
+    }
+    c->need_bytes = off;
+}
+
+static int check_ready(kmc_ctx* c, bool need_centroids) {
+    if (!c) KMC_FAIL(KMC_E_INVALID, "null context");
+    if (!c->ws) KMC_FAIL(KMC_E_STATE, "workspace not bound (kmc_bind_workspace)");
+    if (!c->points && c->n > 0) KMC_FAIL(KMC_E_STATE, "points not bound (kmc_bind_points)");
+    if (need_centroids && !c->have_centroids) KMC_FAIL(KMC_E_STATE, "centroids not set (kmc_set_centroids)");
+    return 0;
+}
+
+// Tensor path: (re)build the split centroid planes if the centroids changed outside kmc_update.
+static int ensure_planes(kmc_ctx* c, cudaStream_t s) {
+    if (c->path != KMC_PATH_TC || c->planes_ready) return 0;
+    KMC_TRY(launch_centroid_absmax(c, s));
+    KMC_TRY(launch_prep_centroids(c, s));
+    c->planes_ready = true;
+    return 0;
+}
+
+static int prof_mark(kmc_ctx* c, int slot, int which, cudaStream_t s) {
+    if (!c->profile) return 0;
+    cudaEvent_t& e = c->prof_ev[slot % kmc_ctx::kProfRing][which];
+    if (!e) KMC_CUDA(cudaEventCreate(&e));
+    KMC_CUDA(cudaEventRecord(e, s));
+    return 0;
+}
+
+// labels of every row; `slot` >= 0 brackets the assign kernel and the refine with profile events
+static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -1) {
+    switch (c->path) {
+        case KMC_PATH_SMALL:
+            return launch_small(c, false, labels, s);
+        case KMC_PATH_SIMT:
+            KMC_TRY(launch_simt_assign(c, nullptr, nullptr, c->n, labels, s));
+            if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
+            return 0;
+        case KMC_PATH_TC:
+            KMC_TRY(ensure_planes(c, s));
+            if (slot >= 0) KMC_TRY(prof_mark(c, slot, 0, s));    // after plane prep, before the tensor kernel
+            KMC_TRY(launch_tc_assign(c, labels, c->perm(), nullptr, s));
+            if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
+            return launch_simt_assign(c, c->perm(), &c->stats()->n_ambiguous, 0, labels, s);
+    }
+    KMC_FAIL(KMC_E_INVALID, "bad kernel path %d", c->path);
+}
+
+static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
+    const size_t kMin = (size_t)8 << 20;
+    if (bytes < 2 * kMin) { memcpy(dst, src, bytes); return; }
+    unsigned nt = std::thread::hardware_concurrency();
+    nt = nt == 0 ? 1 : (nt > 8 ? 8 : nt);
+    if (bytes / nt < kMin) nt = (unsigned)(bytes / kMin);
+    std::vector<std::thread> th;
+    const size_t per = (bytes / nt + 63) & ~(size_t)63;
+    for (unsigned t = 0; t < nt; ++t) {
+        const size_t b = (size_t)t * per;
+        if (b >= bytes) break;
+        const size_t len = (b + per > bytes) ? bytes - b : per;
+        th.emplace_back([=] { memcpy((char*)dst + b, (const char*)src + b, len); });
+    }
+    for (auto& t : th) t.join();
+}
+
+}  // namespace kmc
+
+using namespace kmc;
+
+extern "C" {
+
+int kmc_version(void) { return 1000; }
+
+const char* kmc_last_error(void) { return g_last_error.c_str(); }
+
+int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, uint32_t flags) {
+    if (!out) KMC_FAIL(KMC_E_INVALID, "out is null");
+    *out = nullptr;
+    if (n_rows < 0 || D < 1 || K < 1) KMC_FAIL(KMC_E_INVALID, "need n_rows >= 0, D >= 1, K >= 1");
+    if (n_rows >= ((int64_t)1 << 31)) KMC_FAIL(KMC_E_INVALID, "at most 2^31-1 rows per shard");
+    if (K * D >= ((int64_t)1 << 31)) KMC_FAIL(KMC_E_INVALID, "K*D too large");
+    KMC_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    KMC_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        KMC_FAIL(KMC_E_DEVICE, "device %d is sm_%d%d; this library contains sm_100a code only (no fallback)",
+                 device, prop.major, prop.minor);
+    kmc_ctx* c = new (std::nothrow) kmc_ctx();
+    if (!c) KMC_FAIL(KMC_E_NOMEM, "host allocation failed");
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->n = n_rows; c->D = D; c->K = K; c->flags = flags;
+    int path = (int)(flags & KMC_PATH_MASK);
+    if (path == KMC_PATH_AUTO) {
+        if (small_path_supported(K, D)) path = KMC_PATH_SMALL;
+        else if (tc_path_supported(K, D) && K * D >= 4096) path = KMC_PATH_TC;
+        else path = KMC_PATH_SIMT;
+    } else if (path == KMC_PATH_SMALL && !small_path_supported(K, D)) {
+        delete c;
+        KMC_FAIL(KMC_E_UNSUPPORTED, "small path needs D <= 8 and K*(D+1) <= 384");
+    } else if (path == KMC_PATH_TC && !tc_path_supported(K, D)) {
+        delete c;
+        KMC_FAIL(KMC_E_UNSUPPORTED, "tensor path needs 16 <= D <= 256 and K >= 32");
+    } else if (path != KMC_PATH_SMALL && path != KMC_PATH_SIMT && path != KMC_PATH_TC) {
+        delete c;
+        KMC_FAIL(KMC_E_INVALID, "unknown kernel path flag 0x%x", path);
+    }
+    c->path = path;
+    if (path == KMC_PATH_TC) {
+        c->D_pad = round_up(D, kTcChunkK);
+        if (c->D_pad == 3 * kTcChunkK) c->D_pad = 4 * kTcChunkK;
+        c->K_pad = round_up(K, kTcBlockN);
+        // error of one score relative to |X'_i|*|C'_k|: operand split (3 * 2^-22) plus one
+        // truncation of the fp32 accumulator per MMA k-step, with 25% head-room
+        const double steps = 3.0 * (double)(c->D_pad / 16);
+        c->tc_gamma = 1.25 * (steps + 6.0) / 8388608.0;
+    }
+    layout_workspace(c);
+    *out = c;
+    return 0;
+}
+
+void kmc_destroy(kmc_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    for (int i = 0; i < 2; ++i) {
+        if (c->pinned[i]) cudaFreeHost(c->pinned[i]);
+        if (c->pinned_free[i]) cudaEventDestroy(c->pinned_free[i]);
+        if (c->dev_stage[i]) cudaFree(c->dev_stage[i]);
+    }
+    for (auto& ring : c->prof_ev)
+        for (auto& e : ring)
+            if (e) cudaEventDestroy(e);
+    delete c;
+}
+
+int64_t kmc_workspace_bytes(const kmc_ctx* c) { return c ? c->need_bytes : 0; }
+
+int kmc_bind_workspace(kmc_ctx* c, void* dev_workspace, int64_t bytes) {
+    if (!c || !dev_workspace) KMC_FAIL(KMC_E_INVALID, "null argument");
+    if (bytes < c->need_bytes)
+        KMC_FAIL(KMC_E_NOMEM, "workspace of %lld bytes given, %lld needed", (long long)bytes, (long long)c->need_bytes);
+    if (reinterpret_cast<uintptr_t>(dev_workspace) & 255) KMC_FAIL(KMC_E_INVALID, "workspace must be 256-byte aligned");
+    KMC_CUDA(cudaSetDevice(c->device));
+    c->ws = static_cast<char*>(dev_workspace);
+    c->ws_bytes = bytes;
+    KMC_CUDA(cudaMemset(c->stats(), 0, sizeof(DeviceStats)));
+    c->have_centroids = false;
+    c->planes_ready = false;
+    c->tmaps_ready = false;
+    return 0;
+}
+
+int kmc_bind_points(kmc_ctx* c, const float* dev_points, void* stream) {
+    if (!c) KMC_FAIL(KMC_E_INVALID, "null context");
+    if (!c->ws) KMC_FAIL(KMC_E_STATE, "bind the workspace before the points");
+    if (!dev_points && c->n > 0) KMC_FAIL(KMC_E_INVALID, "null points");
+    if (reinterpret_cast<uintptr_t>(dev_points) & 3) KMC_FAIL(KMC_E_INVALID, "points must be 4-byte aligned");
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    c->points = dev_points;
+    c->planes_ready = false;
+    if (c->path == KMC_PATH_TC) {
+        KMC_CUDA(cudaMemsetAsync(&c->stats()->x_absmax_bits, 0, sizeof(unsigned int), s));
+        KMC_TRY(launch_absmax(c, dev_points, c->n * c->D, &c->stats()->x_absmax_bits, s));
+        KMC_TRY(launch_split_points(c, s));
+        KMC_TRY(tc_setup_tensor_maps(c));
+    }
+    return 0;
+}
+
+int kmc_stage_points(kmc_ctx* c, float* dev_dst, const void* host_src, int src_dtype, int64_t row0,
+                     int64_t n_rows, void* stream) {
+    if (!c || (!dev_dst && n_rows > 0) || (!host_src && n_rows > 0)) KMC_FAIL(KMC_E_INVALID, "null argument");
+    if (src_dtype != KMC_DTYPE_F32 && src_dtype != KMC_DTYPE_F64) KMC_FAIL(KMC_E_INVALID, "bad src_dtype %d", src_dtype);
+    if (n_rows <= 0) return 0;
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const size_t esz = src_dtype == KMC_DTYPE_F64 ? 8 : 4;
+    const char* src = static_cast<const char*>(host_src) + (size_t)row0 * c->D * esz;
+    const int64_t count = n_rows * c->D;
+
+    cudaPointerAttributes attr;
+    bool src_pinned = false;
+    if (cudaPointerGetAttributes(&attr, src) == cudaSuccess) src_pinned = (attr.type == cudaMemoryTypeHost);
+    cudaGetLastError();   // a pageable pointer may leave a sticky-free error code behind
+
+    if (src_pinned && src_dtype == KMC_DTYPE_F32) {
+        KMC_CUDA(cudaMemcpyAsync(dev_dst, src, (size_t)count * 4, cudaMemcpyHostToDevice, s));
+        KMC_CUDA(cudaStreamSynchronize(s));
+        return 0;
+    }
+    const int64_t kChunk = (int64_t)64 << 20;   // bytes per pinned buffer
+    if (!c->pinned[0]) {
+        for (int i = 0; i < 2; ++i) {
+            KMC_CUDA(cudaHostAlloc(&c->pinned[i], (size_t)kChunk, cudaHostAllocDefault));
+            KMC_CUDA(cudaEventCreateWithFlags(&c->pinned_free[i], cudaEventDisableTiming));
+        }
+        c->stage_bytes = kChunk;
+    }
+    if (src_dtype == KMC_DTYPE_F64 && !c->dev_stage[0]) {
+        for (int i = 0; i < 2; ++i) KMC_CUDA(cudaMalloc(&c->dev_stage[i], (size_t)kChunk));
+    }
+    const int64_t elems_per_chunk = kChunk / (int64_t)esz;
+    int b = 0;
+    for (int64_t e0 = 0; e0 < count; e0 += elems_per_chunk, b ^= 1) {
+        const int64_t ne = (count - e0 < elems_per_chunk) ? count - e0 : elems_per_chunk;
+        KMC_CUDA(cudaEventSynchronize(c->pinned_free[b]));
+        if (src_pinned) {
+            // pinned fp64 source: DMA straight from the caller's buffer
+            KMC_CUDA(cudaMemcpyAsync(c->dev_stage[b], src + (size_t)e0 * esz, (size_t)ne * esz, cudaMemcpyHostToDevice, s));
+        } else {
+            parallel_memcpy(c->pinned[b], src + (size_t)e0 * esz, (size_t)ne * esz);
+            void* dst = (src_dtype == KMC_DTYPE_F64) ? c->dev_stage[b] : (void*)(dev_dst + e0);
+            KMC_CUDA(cudaMemcpyAsync(dst, c->pinned[b], (size_t)ne * esz, cudaMemcpyHostToDevice, s));
+        }
+        if (src_dtype == KMC_DTYPE_F64) {
+            KMC_TRY(launch_convert_f64(static_cast<const double*>(c->dev_stage[b]), dev_dst + e0, ne, s));
+            c->launches++;
+        }
+        KMC_CUDA(cudaEventRecord(c->pinned_free[b], s));
+    }
+    if (src_pinned) KMC_CUDA(cudaStreamSynchronize(s));
+    return 0;
+}
+
+int kmc_set_centroids(kmc_ctx* c, const float* host_centroids, void* stream) {
+    if (!c || !host_centroids) KMC_FAIL(KMC_E_INVALID, "null argument");
+    if (!c->ws) KMC_FAIL(KMC_E_STATE, "workspace not bound");
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    KMC_CUDA(cudaMemcpyAsync(c->centroids(), host_centroids, (size_t)(c->K * c->D) * 4, cudaMemcpyHostToDevice, s));
+    KMC_CUDA(cudaStreamSynchronize(s));
+    c->have_centroids = true;
+    c->planes_ready = false;
+    return 0;
+}
+
+int kmc_get_centroids(kmc_ctx* c, float* host_centroids, void* stream) {
+    if (!c || !host_centroids) KMC_FAIL(KMC_E_INVALID, "null argument");
+    if (!c->ws || !c->have_centroids) KMC_FAIL(KMC_E_STATE, "no centroids yet");
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    KMC_CUDA(cudaMemcpyAsync(host_centroids, c->centroids(), (size_t)(c->K * c->D) * 4, cudaMemcpyDeviceToHost, s));
+    KMC_CUDA(cudaStreamSynchronize(s));
+    return 0;
+}
+
+float* kmc_centroids_ptr(kmc_ctx* c) { return (c && c->ws) ? c->centroids() : nullptr; }
+double* kmc_partials_ptr(kmc_ctx* c) { return (c && c->ws) ? c->partials() : nullptr; }
+int64_t kmc_partials_len(const kmc_ctx* c) { return c ? c->K * c->D + c->K + 2 : 0; }
+
+int kmc_accumulate(kmc_ctx* c, void* stream) {
+    KMC_TRY(check_ready(c, true));
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    KMC_CUDA(cudaMemsetAsync(c->partials(), 0, (size_t)kmc_partials_len(c) * 8, s));
+    if (c->n == 0) return 0;
+    const int slot = c->prof_acc_n;
+    KMC_TRY(prof_mark(c, slot, 0, s));
+    if (c->path == KMC_PATH_SMALL) {
+        KMC_TRY(launch_small(c, true, nullptr, s));
+        KMC_TRY(prof_mark(c, slot, 1, s));
+        KMC_TRY(prof_mark(c, slot, 2, s));
+    } else {
+        KMC_TRY(assign_into(c, c->labels(), s, slot));
+        KMC_TRY(prof_mark(c, slot, 2, s));
+        KMC_TRY(launch_sorted_accumulate(c, c->labels(), s));
+    }
+    KMC_TRY(prof_mark(c, slot, 3, s));
+    if (c->profile) c->prof_acc_n++;
+    return 0;
+}
+
+int kmc_update(kmc_ctx* c, void* stream) {
+    KMC_TRY(check_ready(c, true));
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int slot = c->prof_upd_n;
+    KMC_TRY(prof_mark(c, slot, 4, s));
+    KMC_TRY(launch_update(c, s));
+    if (c->path == KMC_PATH_TC) {
+        KMC_TRY(launch_prep_centroids(c, s));   // update_kernel refreshed c_absmax
+        c->planes_ready = true;
+    }
+    KMC_TRY(prof_mark(c, slot, 5, s));
+    if (c->profile) c->prof_upd_n++;
+    return 0;
+}
+
+int kmc_read_stats(kmc_ctx* c, double* host_stats, void* stream) {
+    if (!c || !host_stats) KMC_FAIL(KMC_E_INVALID, "null argument");
+    if (!c->ws) KMC_FAIL(KMC_E_STATE, "workspace not bound");
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    DeviceStats st;
+    double inertia = 0.0;
+    KMC_CUDA(cudaMemcpyAsync(&st, c->stats(), sizeof(st), cudaMemcpyDeviceToHost, s));
+    KMC_CUDA(cudaMemcpyAsync(&inertia, c->partials() + c->K * c->D + c->K, 8, cudaMemcpyDeviceToHost, s));
+    KMC_CUDA(cudaStreamSynchronize(s));
+    if (st.watchdog) KMC_FAIL(KMC_E_DEVICE, "tensor kernel barrier wait timed out (code 0x%x)", st.watchdog);
+    for (int i = 0; i < KMC_STAT_COUNT; ++i) host_stats[i] = 0.0;
+    host_stats[KMC_STAT_INERTIA] = inertia;
+    host_stats[KMC_STAT_SHIFT2] = st.shift2;
+    host_stats[KMC_STAT_AMBIGUOUS] = (double)st.n_ambiguous;
+    host_stats[KMC_STAT_KERNEL_PATH] = (double)c->path;
+    host_stats[KMC_STAT_LAUNCHES] = (double)c->launches;
+    return 0;
+}
+
+int kmc_iterate(kmc_ctx* c, int max_iters, double tol, int* n_iter_out, double* inertia_out,
+                double* shift2_out, void* stream) {
+    KMC_TRY(check_ready(c, true));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    int it = 0;
+    for (; it < max_iters;) {
+        KMC_TRY(kmc_accumulate(c, stream));
+        KMC_TRY(kmc_update(c, stream));
+        ++it;
+        if (tol > 0.0) {
+            double shift2 = 0.0;
+            KMC_CUDA(cudaMemcpyAsync(&shift2, &c->stats()->shift2, 8, cudaMemcpyDeviceToHost, s));
+            KMC_CUDA(cudaStreamSynchronize(s));
+            if (shift2 <= tol) break;
+        }
+    }
+    double st[KMC_STAT_COUNT];
+    KMC_TRY(kmc_read_stats(c, st, stream));
+    if (n_iter_out) *n_iter_out = it;
+    if (inertia_out) *inertia_out = st[KMC_STAT_INERTIA];
+    if (shift2_out) *shift2_out = st[KMC_STAT_SHIFT2];
+    return 0;
+}
+
+int kmc_assign(kmc_ctx* c, int32_t* dev_labels, void* stream) {
+    KMC_TRY(check_ready(c, true));
+    if (!dev_labels && c->n > 0) KMC_FAIL(KMC_E_INVALID, "null labels");
+    if (c->n == 0) return 0;
+    KMC_CUDA(cudaSetDevice(c->device));
+    return assign_into(c, dev_labels, static_cast<cudaStream_t>(stream));
+}
+
+int kmc_set_param(kmc_ctx* c, int param, double value) {
+    if (!c) KMC_FAIL(KMC_E_INVALID, "null context");
+    switch (param) {
+        case KMC_PARAM_TC_GAMMA:
+            if (!(value >= 0.0)) KMC_FAIL(KMC_E_INVALID, "gamma must be >= 0");
+            c->tc_gamma = value;
+            return 0;
+        case KMC_PARAM_PROFILE:
+            c->profile = value != 0.0;
+            c->prof_acc_n = c->prof_upd_n = 0;
+            return 0;
+    }
+    KMC_FAIL(KMC_E_INVALID, "unknown parameter %d", param);
+}
+
+int kmc_get_phase_ms(kmc_ctx* c, float* out_ms, int n) {
+    if (!c || !out_ms || n < 1) KMC_FAIL(KMC_E_INVALID, "bad argument");
+    KMC_CUDA(cudaSetDevice(c->device));
+    double sum[4] = {0, 0, 0, 0};
+    const int na = c->prof_acc_n < kmc_ctx::kProfRing ? c->prof_acc_n : kmc_ctx::kProfRing;
+    const int nu = c->prof_upd_n < kmc_ctx::kProfRing ? c->prof_upd_n : kmc_ctx::kProfRing;
+    for (int i = 0; i < na; ++i) {
+        const int slot = (c->prof_acc_n - 1 - i) % kmc_ctx::kProfRing;
+        cudaEvent_t* e = c->prof_ev[slot];
+        KMC_CUDA(cudaEventSynchronize(e[3]));
+        float ms = 0.f;
+        KMC_CUDA(cudaEventElapsedTime(&ms, e[0], e[1])); sum[0] += ms;
+        KMC_CUDA(cudaEventElapsedTime(&ms, e[1], e[2])); sum[1] += ms;
+        KMC_CUDA(cudaEventElapsedTime(&ms, e[2], e[3])); sum[2] += ms;
+    }
+    for (int i = 0; i < nu; ++i) {
+        const int slot = (c->prof_upd_n - 1 - i) % kmc_ctx::kProfRing;
+        cudaEvent_t* e = c->prof_ev[slot];
+        KMC_CUDA(cudaEventSynchronize(e[5]));
+        float ms = 0.f;
+        KMC_CUDA(cudaEventElapsedTime(&ms, e[4], e[5])); sum[3] += ms;
+    }
+    const float vals[KMC_PHASE_COUNT] = {na ? (float)(sum[0] / na) : 0.f, na ? (float)(sum[1] / na) : 0.f,
+                                         na ? (float)(sum[2] / na) : 0.f, nu ? (float)(sum[3] / nu) : 0.f,
+                                         (float)na};
+    for (int i = 0; i < n && i < KMC_PHASE_COUNT; ++i) out_ms[i] = vals[i];
+    c->prof_acc_n = c->prof_upd_n = 0;
+    return 0;
+}
+
+int kmc_debug_tc_scores(kmc_ctx* c, float* dev_scores, void* stream) {
+    KMC_TRY(check_ready(c, true));
+    if (c->path != KMC_PATH_TC) KMC_FAIL(KMC_E_UNSUPPORTED, "context is not on the tensor path");
+    if (!dev_scores) KMC_FAIL(KMC_E_INVALID, "null scores");
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    KMC_TRY(ensure_planes(c, s));
+    return launch_tc_assign(c, c->labels(), nullptr, dev_scores, s);
+}
+
+}  // extern "C"

@@ -1,0 +1,131 @@
+// Shared declarations of libkmc_b200 (sm_100a only).  See include/kmc.h for the C ABI.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/kmc.h"
+
+namespace kmc {
+
+void set_error(const char* fmt, ...);
+
+#define KMC_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            kmc::set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__,          \
+                           cudaGetErrorString(e__));                                     \
+            return (int)e__;                                                             \
+        }                                                                                \
+    } while (0)
+
+#define KMC_TRY(call)                                                                    \
+    do {                                                                                 \
+        int r__ = (call);                                                                \
+        if (r__ != 0) return r__;                                                        \
+    } while (0)
+
+#define KMC_FAIL(code, ...)                                                              \
+    do {                                                                                 \
+        kmc::set_error(__VA_ARGS__);                                                     \
+        return (code);                                                                   \
+    } while (0)
+
+constexpr int kTcBlockM = 128;   // rows per tensor tile (TMEM lanes)
+constexpr int kTcBlockN = 256;   // centroids per tensor tile (TMEM columns of one accumulator)
+constexpr int kTcChunkK = 64;    // fp16 elements per 128-byte swizzle row
+constexpr int kStatSlots = 16;
+
+// Device-resident scalars written by kernels (all doubles / 64-bit so one memset clears them).
+struct DeviceStats {
+    double inertia;        // last accumulate
+    double shift2;         // last update
+    unsigned long long n_ambiguous;   // rows in the refine worklist (last tensor pass)
+    unsigned int x_absmax_bits;       // max |x| over the shard (fp32 bits), set at bind time
+    unsigned int c_absmax_bits;       // max |c| after the last update / set_centroids
+    unsigned int c_normmax_bits;      // max_k |C'_k| in scaled units (prep kernel)
+    unsigned int watchdog;            // non-zero: a tensor-kernel barrier wait timed out
+    float sigma_x;                    // power-of-two scale of the point planes
+    float sigma_c;                    // power-of-two scale of the centroid planes (x -2 folded)
+    unsigned long long pad[2];
+};
+
+}  // namespace kmc
+
+struct kmc_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int64_t n = 0, D = 0, K = 0;
+    uint32_t flags = 0;
+    int path = 0;                       // KMC_PATH_*
+    // tensor-path geometry
+    int64_t D_pad = 0, K_pad = 0;
+    double tc_gamma = 0.0;
+    // workspace
+    char* ws = nullptr;
+    int64_t ws_bytes = 0;
+    int64_t need_bytes = 0;
+    int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_perm = 0,
+            off_hist = 0, off_offsets = 0, off_cursor = 0, off_segoff = 0,
+            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0,
+            off_sums_zero_bytes = 0;
+    const float* points = nullptr;
+    bool have_centroids = false;
+    bool planes_ready = false;
+    // tensor maps (opaque 128-byte blobs, 64-byte aligned)
+    alignas(64) CUtensorMap tmap_xhi;
+    alignas(64) CUtensorMap tmap_xlo;
+    alignas(64) CUtensorMap tmap_c;
+    bool tmaps_ready = false;
+    // pinned staging
+    void* pinned[2] = {nullptr, nullptr};
+    cudaEvent_t pinned_free[2] = {nullptr, nullptr};
+    void* dev_stage[2] = {nullptr, nullptr};
+    int64_t stage_bytes = 0;
+    // optional phase timing: ring of event sextuples (acc: e0..e3, update: e4,e5)
+    bool profile = false;
+    static constexpr int kProfRing = 32;
+    cudaEvent_t prof_ev[kProfRing][6] = {};
+    int prof_acc_n = 0, prof_upd_n = 0;
+    // bookkeeping
+    int64_t launches = 0;
+    double host_stats[KMC_STAT_COUNT] = {0};
+
+    template <typename T> T* at(int64_t off) const { return reinterpret_cast<T*>(ws + off); }
+    float* centroids() const { return at<float>(off_centroids); }
+    double* partials() const { return at<double>(off_partials); }
+    kmc::DeviceStats* stats() const { return at<kmc::DeviceStats>(off_stats); }
+    int32_t* labels() const { return at<int32_t>(off_labels); }
+    int32_t* perm() const { return at<int32_t>(off_perm); }
+};
+
+namespace kmc {
+
+// ---- kernels (one .cu each) -------------------------------------------------------------------
+// stage.cu
+int launch_convert_f64(const double* src, float* dst, int64_t count, cudaStream_t s);
+int launch_absmax(kmc_ctx* c, const float* x, int64_t count, unsigned int* out_bits, cudaStream_t s);
+int launch_split_points(kmc_ctx* c, cudaStream_t s);
+// assign_small.cu
+bool small_path_supported(int64_t K, int64_t D);
+int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s);
+// assign_simt.cu
+int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long long* n_work_dev,
+                       int64_t n_work_host, int32_t* labels_out, cudaStream_t s);
+// assign_tc.cu
+bool tc_path_supported(int64_t K, int64_t D);
+int tc_setup_tensor_maps(kmc_ctx* c);
+int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, float* scores_out, cudaStream_t s);
+// accumulate.cu
+int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s);
+// update.cu
+int launch_update(kmc_ctx* c, cudaStream_t s);
+int launch_prep_centroids(kmc_ctx* c, cudaStream_t s);
+int launch_centroid_absmax(kmc_ctx* c, cudaStream_t s);
+
+__host__ __device__ inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+}  // namespace kmc

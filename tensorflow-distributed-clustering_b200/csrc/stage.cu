@@ -1,0 +1,99 @@
+// Staging-side kernels: fp64->fp32 conversion of staged chunks, abs-max scan and the one-time
+// split of the resident fp32 points into the two scaled fp16 planes the tcgen05 kernel reads.
+//
+// Reference: the data lands on the GPU through `X = tf.Variable(X_mat)` + initializer run
+// (scripts/distribuitedClustering.py:217, :273); there is no counterpart of the split planes.
+#include "kmc_common.cuh"
+#include "kmc_device.cuh"
+
+namespace kmc {
+
+__global__ void __launch_bounds__(256) convert_f64_kernel(const double* __restrict__ src,
+                                                          float* __restrict__ dst, int64_t count) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < count; i += stride) dst[i] = (float)src[i];
+}
+
+int launch_convert_f64(const double* src, float* dst, int64_t count, cudaStream_t s) {
+    if (count <= 0) return 0;
+    int64_t blocks = (count + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    convert_f64_kernel<<<(unsigned)blocks, 256, 0, s>>>(src, dst, count);
+    KMC_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// max |x| over a flat fp32 array (NaNs ignored), folded into *out_bits with atomicMax on the
+// bit pattern (non-negative floats order like unsigned ints).
+__global__ void __launch_bounds__(256) absmax_kernel(const float* __restrict__ x, int64_t count,
+                                                     unsigned int* __restrict__ out_bits) {
+    float m = 0.f;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
+    const int64_t nvec = vec_ok ? count / 4 : 0;
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    for (int64_t i = tid; i < nvec; i += stride) {
+        float4 v = ld_stream_f4(x4 + i);
+        m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+    }
+    for (int64_t i = nvec * 4 + tid; i < count; i += stride) m = fmaxf(m, fabsf(x[i]));
+    m = warp_max(m);
+    if ((threadIdx.x & 31) == 0 && m > 0.f && m < INFINITY) atomicMax(out_bits, __float_as_uint(m));
+}
+
+int launch_absmax(kmc_ctx* c, const float* x, int64_t count, unsigned int* out_bits, cudaStream_t s) {
+    if (count <= 0) return 0;
+    int64_t blocks = (count / 4 + 255) / 256 + 1;
+    const int64_t cap = (int64_t)c->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    absmax_kernel<<<(unsigned)blocks, 256, 0, s>>>(x, count, out_bits);
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+// One warp per row: X'_hi = fp16(x * sigma), X'_lo = fp16(x * sigma - X'_hi) (both at the same
+// scale), zero padding up to D_pad, and xnorm'[row] = |x * sigma| rounded up.
+__global__ void __launch_bounds__(256) split_points_kernel(const float* __restrict__ x, int64_t n, int D,
+                                                           int D_pad, __half* __restrict__ xhi,
+                                                           __half* __restrict__ xlo,
+                                                           float* __restrict__ xnorm, DeviceStats* stats) {
+    const float sigma = scale_from_absmax(__uint_as_float(stats->x_absmax_bits));
+    if (blockIdx.x == 0 && threadIdx.x == 0) stats->sigma_x = sigma;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = warp; row < n; row += nwarps) {
+        const float* xr = x + row * (int64_t)D;
+        __half* hr = xhi + row * (int64_t)D_pad;
+        __half* lr = xlo + row * (int64_t)D_pad;
+        float ss = 0.f;
+        for (int j = lane; j < D_pad; j += 32) {
+            float v = (j < D) ? xr[j] * sigma : 0.f;
+            __half h = __float2half_rn(v);
+            float r = v - __half2float(h);          // exact
+            hr[j] = h;
+            lr[j] = __float2half_rn(r);
+            ss = fmaf(v, v, ss);
+        }
+        ss = warp_sum(ss);
+        if (lane == 0) xnorm[row] = sqrtf(ss) * 1.001f;
+    }
+}
+
+int launch_split_points(kmc_ctx* c, cudaStream_t s) {
+    int64_t blocks = (c->n + 7) / 8;
+    const int64_t cap = (int64_t)c->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    split_points_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->points, c->n, (int)c->D, (int)c->D_pad,
+                                                         c->at<__half>(c->off_xhi), c->at<__half>(c->off_xlo),
+                                                         c->at<float>(c->off_xnorm), c->stats());
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+}  // namespace kmc

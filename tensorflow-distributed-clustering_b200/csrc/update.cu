@@ -1,0 +1,142 @@
+// Centroid update + convergence statistics, and (tensor path) the per-iteration preparation of
+// the split fp16 centroid planes.
+//
+// Replaces reference scripts/distribuitedClustering.py:257-263: add_n of the per-GPU partials
+// (done before this kernel by the host's all-reduce), tile/reshape/div/transpose and the assign
+// of `global_centroids` on /cpu:0.  The division is done in fp64 like the reference and rounded
+// once to fp32.  A globally empty cluster keeps its centroid (KMC_EMPTY_KEEP) or becomes NaN
+// (KMC_EMPTY_NAN, the reference's 0/0).
+#include "kmc_common.cuh"
+#include "kmc_device.cuh"
+
+namespace kmc {
+
+__global__ void __launch_bounds__(256) update_kernel(float* __restrict__ cent, const double* __restrict__ partials,
+                                                     int K, int D, int empty_nan, DeviceStats* stats) {
+    const int64_t total = (int64_t)K * D;
+    double shift = 0.0;
+    float amax = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int k = (int)(i / D);
+        const double cnt = partials[total + k];
+        const float old = cent[i];
+        float nw;
+        if (cnt > 0.0) nw = (float)(partials[i] / cnt);
+        else nw = empty_nan ? __int_as_float(0x7fc00000) : old;
+        cent[i] = nw;
+        const double d = (double)nw - (double)old;
+        if (d == d) shift += d * d;
+        amax = fmaxf(amax, fabsf(nw));
+    }
+    shift = warp_sum(shift);
+    amax = warp_max(amax);
+    if ((threadIdx.x & 31) == 0) {
+        if (shift != 0.0) atomicAdd(&stats->shift2, shift);
+        if (amax > 0.f && amax < INFINITY) atomicMax(&stats->c_absmax_bits, __float_as_uint(amax));
+    }
+}
+
+int launch_update(kmc_ctx* c, cudaStream_t s) {
+    const int64_t total = c->K * c->D;
+    int64_t blocks = (total + 255) / 256;
+    const int64_t cap = (int64_t)c->sm_count * 4;
+    blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+    // shift2 and c_absmax restart at zero for every update
+    KMC_CUDA(cudaMemsetAsync(&c->stats()->shift2, 0, sizeof(double), s));
+    KMC_CUDA(cudaMemsetAsync(&c->stats()->c_absmax_bits, 0, sizeof(unsigned int), s));
+    update_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), c->partials(), (int)c->K, (int)c->D,
+                                                   (c->flags & KMC_EMPTY_NAN) ? 1 : 0, c->stats());
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+__global__ void __launch_bounds__(256) centroid_absmax_kernel(const float* __restrict__ cent, int64_t total,
+                                                              DeviceStats* stats) {
+    float amax = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x)
+        amax = fmaxf(amax, fabsf(cent[i]));
+    amax = warp_max(amax);
+    if ((threadIdx.x & 31) == 0 && amax > 0.f && amax < INFINITY)
+        atomicMax(&stats->c_absmax_bits, __float_as_uint(amax));
+}
+
+int launch_centroid_absmax(kmc_ctx* c, cudaStream_t s) {
+    const int64_t total = c->K * c->D;
+    int64_t blocks = (total + 255) / 256;
+    const int64_t cap = (int64_t)c->sm_count * 4;
+    blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+    KMC_CUDA(cudaMemsetAsync(&c->stats()->c_absmax_bits, 0, sizeof(unsigned int), s));
+    centroid_absmax_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), total, c->stats());
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+// One warp per (padded) centroid row: C'_hi / C'_lo = split fp16 of (-2 * sigma_c * c), and
+// cn'[k] = sigma_x * sigma_c * |c_k|^2 (+inf for padding rows and NaN centroids, so they never
+// win), plus max_k |C'_k| for the refine threshold.
+__global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __restrict__ cent, int K, int D,
+                                                             int K_pad, int D_pad, __half* __restrict__ chi,
+                                                             __half* __restrict__ clo, float* __restrict__ cnorm,
+                                                             DeviceStats* stats) {
+    // 2*|c| < 2^14 after scaling: absmax of (2c)
+    const float sigma_c = scale_from_absmax(2.f * __uint_as_float(stats->c_absmax_bits));
+    const float sigma_x = stats->sigma_x;
+    if (blockIdx.x == 0 && threadIdx.x == 0) stats->sigma_c = sigma_c;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    float nmax = 0.f;
+    for (int k = warp; k < K_pad; k += nwarps) {
+        __half* hr = chi + (int64_t)k * D_pad;
+        __half* lr = clo + (int64_t)k * D_pad;
+        double ss = 0.0;
+        float ss_scaled = 0.f;
+        if (k < K) {
+            for (int j = lane; j < D; j += 32) {
+                const float cval = cent[(int64_t)k * D + j];
+                const float v = -2.f * sigma_c * cval;
+                ss += (double)cval * (double)cval;
+                ss_scaled = fmaf(v, v, ss_scaled);
+            }
+        }
+        ss = warp_sum(ss);
+        ss_scaled = warp_sum(ss_scaled);
+        float cn = (float)(ss * (double)sigma_x * (double)sigma_c);
+        // padding rows, NaN / infinite centroids: zero planes and an infinite norm -> never chosen
+        const bool dead = (k >= K) || !(cn < INFINITY) || !(ss_scaled < INFINITY);
+        for (int j = lane; j < D_pad; j += 32) {
+            float v = 0.f;
+            if (!dead && j < D) v = -2.f * sigma_c * cent[(int64_t)k * D + j];
+            const __half h = __float2half_rn(v);
+            const float r = v - __half2float(h);
+            hr[j] = h;
+            lr[j] = __float2half_rn(r);
+        }
+        if (lane == 0) {
+            cnorm[k] = dead ? INFINITY : cn;
+            if (!dead) nmax = fmaxf(nmax, sqrtf(ss_scaled) * 1.001f);
+        }
+    }
+    if (lane == 0 && nmax > 0.f && nmax < INFINITY) atomicMax(&stats->c_normmax_bits, __float_as_uint(nmax));
+}
+
+int launch_prep_centroids(kmc_ctx* c, cudaStream_t s) {
+    int64_t blocks = (c->K_pad + 7) / 8;
+    const int64_t cap = (int64_t)c->sm_count * 4;
+    blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+    KMC_CUDA(cudaMemsetAsync(&c->stats()->c_normmax_bits, 0, sizeof(unsigned int), s));
+    __half* chi = c->at<__half>(c->off_cplanes);
+    __half* clo = chi + c->K_pad * c->D_pad;
+    prep_centroids_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), (int)c->K, (int)c->D, (int)c->K_pad,
+                                                           (int)c->D_pad, chi, clo, c->at<float>(c->off_cnorm),
+                                                           c->stats());
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+}  // namespace kmc

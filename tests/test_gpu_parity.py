@@ -1,0 +1,234 @@
+"""GPU parity tests (B200): the CUDA path, called through the C ABI (ctypes -> libkmc_b200.so),
+against the float64 oracle on the same seeded inputs and against the committed golden fixtures.
+
+Bar (BASELINE.json north_star): labels identical except rows whose oracle top-2 distances differ
+by <= 1e-5 relative; centroids and inertia within 1e-4 relative at every iteration; counts are
+integers and must match exactly once near-tie rows are set aside.
+"""
+import numpy as np
+import pytest
+
+import oracle
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4          # centroids / inertia, per iteration (north_star)
+TIE_RTOL = 1e-5      # near-tie window for labels (north_star)
+
+
+def _shard(pkg, X, K, device, path="auto", empty="keep"):
+    import torch
+
+    s = pkg.LloydShard(X.shape[0], X.shape[1], K, device, empty=empty, path=path)
+    s.bind_points(torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).to(device))
+    return s
+
+
+def _check_iterations(pkg, X, C0, iters, device, path="auto", n_shards=1, form="diff", hist=None):
+    """Run `iters` Lloyd iterations on the GPU, one C-ABI call per phase, checking every
+    intermediate against the oracle (labels_t, counts_t, inertia_t vs C_t; C_{t+1})."""
+    import torch
+
+    K = C0.shape[0]
+    ranges = pkg.shard_ranges(X.shape[0], n_shards)
+    shards = [_shard(pkg, X[r0:r1], K, device, path) for r0, r1 in ranges]
+    for s in shards:
+        s.set_centroids(C0)
+    C = np.asarray(C0, dtype=np.float64)
+    for t in range(iters):
+        ref = oracle.lloyd_iteration(X, C, n_shards=n_shards, form=form) if hist is None else None
+        if hist is not None:
+            lab_ref, d1, d2 = oracle.assign(X, C, form)
+            ref = {"labels": lab_ref, "d1": d1, "d2": d2, "counts": hist["counts"][t],
+                   "centroids": hist["centroids"][t], "inertia": hist["inertia"][t]}
+            assert np.array_equal(lab_ref, hist["labels"][t])
+        labels = np.concatenate([s.assign().cpu().numpy() for s in shards])
+        bad = oracle.label_mismatches(labels, ref["labels"], ref["d1"], ref["d2"], TIE_RTOL)
+        assert len(bad) == 0, f"iter {t}: {len(bad)} label mismatches outside near-ties, first rows {bad[:5]}"
+        for s in shards:
+            s.accumulate()
+        total = torch.zeros_like(shards[0].partials)
+        for s in shards:
+            total += s.partials
+        for s in shards:
+            s.partials.copy_(total)             # what the all-reduce leaves in every shard
+        part = total.cpu().numpy()
+        counts, inertia = part[K * X.shape[1]:K * X.shape[1] + K], part[K * X.shape[1] + K]
+        n_tie = int(oracle.near_tie_mask(ref["d1"], ref["d2"], TIE_RTOL).sum())
+        assert counts.sum() == X.shape[0]
+        assert np.abs(counts - ref["counts"]).sum() <= 2 * n_tie, f"iter {t}: counts differ beyond near-ties"
+        assert abs(inertia - ref["inertia"]) <= RTOL * abs(ref["inertia"]), (t, inertia, ref["inertia"])
+        for s in shards:
+            s.update()
+        got = shards[0].get_centroids()
+        for s in shards[1:]:
+            assert np.array_equal(s.get_centroids(), got), "replicated centroids diverged"
+        assert oracle.rel_err(got, ref["centroids"]) <= RTOL, (t, oracle.rel_err(got, ref["centroids"]))
+        C = np.asarray(ref["centroids"], dtype=np.float64)
+    stats = shards[0].stats()
+    for s in shards:
+        s.close()
+    return stats
+
+
+GOLDEN_CASES = ["c1_blobs_d2_k8", "c1_blobs_d2_k8_g3", "c2_image_d3_k16", "c3_blobs_d32_k256",
+                "c4_blobs_d128_k1024", "c5_blobs_d64_k4096", "edge_k1_d1", "edge_dup_centroids"]
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_golden_case_per_iteration(name, pkg, golden_index, cuda_device):
+    z, meta = load_golden(name, pkg, golden_index)
+    stats = _check_iterations(pkg, z["X"], z["C0"], meta["iters"], cuda_device, n_shards=meta["shards"],
+                              form=meta["form"], hist=z)
+    want = {"c1": "small", "c2": "small", "c3": "tc", "c4": "tc", "c5": "tc"}.get(name[:2])
+    if want:
+        assert stats["path"] == want
+
+
+@pytest.mark.parametrize("n,d,k,path", [
+    (5000, 2, 8, "small"), (4097, 3, 16, "small"), (3001, 8, 40, "small"), (1, 2, 1, "small"),
+    (3000, 5, 7, "simt"), (2500, 20, 100, "simt"), (2049, 33, 65, "simt"), (4096, 32, 256, "simt"),
+    (4000, 16, 32, "tc"), (3000, 32, 256, "tc"), (2500, 64, 300, "tc"), (2000, 128, 1024, "tc"),
+    (1500, 100, 257, "tc"), (1200, 160, 96, "tc"), (1000, 256, 512, "tc"), (129, 64, 64, "tc"),
+])
+def test_random_shapes_each_path(n, d, k, path, pkg, cuda_device):
+    X, _ = pkg.datagen.blobs_numpy(n, d, max(2, k // 3), seed=n + d + k)
+    stats = _check_iterations(pkg, X, X[:k].copy(), 2, cuda_device, path=path,
+                              form="gemm" if d * k > 20000 else "diff")
+    assert stats["path"] == path
+
+
+def test_unscaled_data_ranges_on_tensor_path(pkg, cuda_device):
+    # tiny and huge magnitudes go through the power-of-two scaling of the fp16 planes
+    for scale in (1e-6, 3e4):
+        X, _ = pkg.datagen.blobs_numpy(3000, 64, 40, seed=17)
+        X = (X * np.float32(scale)).astype(np.float32)
+        _check_iterations(pkg, X, X[:128].copy(), 2, cuda_device, path="tc")
+
+
+def test_tensor_scores_match_fp64(pkg, cuda_device):
+    """The raw tcgen05 scores |c|^2 - 2 x.c against float64, within the bound the kernel uses to
+    decide which rows need the exact refine pass."""
+    for n, d, k in [(300, 64, 256), (1000, 128, 1024), (257, 32, 100), (640, 256, 300)]:
+        X, _ = pkg.datagen.blobs_numpy(n, d, 16, seed=d)
+        C = X[:k].copy() if k <= n else np.concatenate([X] * (k // n + 1))[:k] * np.float32(0.9)
+        s = _shard(pkg, X, k, cuda_device, path="tc")
+        s.set_centroids(C)
+        got = s.debug_tc_scores().cpu().numpy().astype(np.float64)
+        X64, C64 = X.astype(np.float64), C.astype(np.float64)
+        want = (C64 * C64).sum(1)[None, :] - 2.0 * X64 @ C64.T
+        bound = np.linalg.norm(X64, axis=1)[:, None] * (2 * np.linalg.norm(C64, axis=1))[None, :]
+        err = np.abs(got - want) / bound
+        d_pad = {32: 64, 64: 64, 128: 128, 256: 256}[d]
+        gamma = 1.25 * (3 * d_pad / 16 + 6) / 2 ** 23       # the bound kmc_create derives (kmc_api.cu)
+        print(f"tc scores n={n} d={d} k={k}: max rel err {err.max():.3e} (gamma {gamma:.3e})")
+        assert err.max() < gamma, (n, d, k, err.max())
+        s.close()
+
+
+def test_exact_ties_resolve_to_lowest_index_on_every_path(pkg, cuda_device):
+    for d, k, path in [(4, 6, "small"), (20, 12, "simt"), (32, 64, "tc"), (128, 300, "tc")]:
+        X, _ = pkg.datagen.blobs_numpy(2000, d, 5, seed=d)
+        C = X[:k].copy()
+        C[k - 1] = C[0]                      # duplicate centroid: rows nearest to it tie exactly
+        C[3] = C[2]
+        s = _shard(pkg, X, k, cuda_device, path=path)
+        s.set_centroids(C)
+        lab = s.assign().cpu().numpy()
+        ref, d1, d2 = oracle.assign(X, C)
+        assert (ref != k - 1).all() and (ref != 3).all() and (d2 == d1).sum() > 0
+        assert np.array_equal(lab[d2 == d1], ref[d2 == d1])              # exact ties: lowest index
+        assert len(oracle.label_mismatches(lab, ref, d1, d2, TIE_RTOL)) == 0
+        s.close()
+
+
+def test_empty_cluster_policies(pkg, cuda_device):
+    X = np.zeros((64, 2), dtype=np.float32)
+    X[:, 0] = np.arange(64) % 2
+    C0 = np.array([[0.0, 0.0], [1.0, 0.0], [50.0, 50.0]], dtype=np.float32)
+    for empty in ("keep", "nan"):
+        s = _shard(pkg, X, 3, cuda_device, empty=empty)
+        s.set_centroids(C0)
+        s.iterate(2)
+        C = s.get_centroids()
+        assert np.allclose(C[:2], [[0, 0], [1, 0]])
+        assert (np.isnan(C[2]).all() if empty == "nan" else np.array_equal(C[2], C0[2]))
+        s.close()
+
+
+def test_nan_centroid_never_wins(pkg, cuda_device):
+    for d, k, path in [(3, 8, "small"), (24, 16, "simt"), (64, 64, "tc")]:
+        X, _ = pkg.datagen.blobs_numpy(1500, d, 4, seed=2)
+        C = X[:k].copy()
+        C[1] = np.nan
+        s = _shard(pkg, X, k, cuda_device, path=path)
+        s.set_centroids(C)
+        lab = s.assign().cpu().numpy()
+        ref, d1, d2 = oracle.assign(X, C)
+        assert (lab != 1).all()
+        assert len(oracle.label_mismatches(lab, ref, d1, d2, TIE_RTOL)) == 0
+        s.close()
+
+
+def test_host_staging_fp64_fp32_and_batches(pkg, cuda_device):
+    X, _ = pkg.datagen.blobs_numpy(10007, 7, 5, seed=1)
+    for host in (X, X.astype(np.float64)):
+        for batch in (None, 1000, 4096):
+            s = pkg.LloydShard(5000, 7, 5, cuda_device)
+            s.stage_from_host(host, 3000, batch)
+            assert np.array_equal(s.points.cpu().numpy(), X[3000:8000])
+            s.close()
+
+
+def test_drop_in_entry_point_matches_oracle(pkg, cuda_device):
+    X, _ = pkg.datagen.blobs_numpy(20000, 2, 8, seed=123128)
+    X64 = X.astype(np.float64)                       # the reference feeds float64 (make_classification)
+    C0 = X64[:8]
+    res = pkg.distribuited_k_means(X64, 8, ["/device:GPU:0"], C0, 20)          # 5-positional form (:303)
+    ref = oracle.run_lloyd(X, C0, 20)
+    for key in ("end_center", "cluster_idx", "centroids", "init_center", "setup_time", "initialization_time",
+                "computation_time", "n_iter"):
+        assert key in res
+    assert res["n_iter"] == 20 and res["cluster_idx"].dtype == np.int64
+    assert oracle.rel_err(res["end_center"], ref["end_center"]) <= RTOL
+    assert len(oracle.label_mismatches(res["cluster_idx"], ref["cluster_idx"], ref["final_d1"], ref["final_d2"])) == 0
+    assert abs(res["inertia"] - ref["history"][-1]["inertia"]) <= RTOL * ref["history"][-1]["inertia"]
+    assert np.array_equal(res["centroids"], res["cluster_idx"])                 # one GPU: last shard = all rows
+    # HEAD's 4-positional form (:180): centres from seeded k-means++
+    res4 = pkg.distribuited_k_means(X, 8, 1, 5, seed=3)
+    assert res4["n_iter"] == 5 and res4["init_center"].shape == (8, 2)
+    ref4 = oracle.run_lloyd(X, res4["init_center"], 5)
+    assert oracle.rel_err(res4["end_center"], ref4["end_center"]) <= RTOL
+    # tolerance-based early stop (this project's addition)
+    res_tol = pkg.distribuited_k_means(X, 8, 1, C0, 200, tol=1e-12)
+    assert res_tol["converged"] and res_tol["n_iter"] < 200
+
+
+def test_size_independent_properties_large(pkg, cuda_device):
+    """A larger tensor-path run checked through properties that need no full oracle pass:
+    counts sum to N, the per-cluster sums add up to the column sums of X (linearity), the label
+    pass is idempotent, and a random row sample agrees with the oracle."""
+    import torch
+
+    n, d, k = 1 << 20, 128, 1024
+    X, _ = pkg.datagen.blobs_torch(n, d, k, seed=123128, device=cuda_device)
+    C0 = X[:k].cpu().numpy()
+    s = pkg.LloydShard(n, d, k, cuda_device)
+    s.bind_points(X)
+    s.set_centroids(C0)
+    lab1 = s.assign().clone()
+    lab2 = s.assign()
+    assert torch.equal(lab1, lab2)
+    s.accumulate()
+    part = s.partials.cpu().numpy()
+    sums, counts = part[:k * d].reshape(k, d), part[k * d:k * d + k]
+    assert counts.sum() == n
+    assert np.array_equal(counts, np.bincount(lab1.cpu().numpy(), minlength=k))
+    col = X.double().sum(0).cpu().numpy()
+    assert np.max(np.abs(sums.sum(0) - col)) <= 1e-6 * np.max(np.abs(col))
+    idx = np.random.default_rng(0).choice(n, 4096, replace=False)
+    ref, d1, d2 = oracle.assign(X[torch.from_numpy(idx).to(cuda_device)].cpu().numpy(), C0, "gemm")
+    assert len(oracle.label_mismatches(lab1.cpu().numpy()[idx], ref, d1, d2, TIE_RTOL)) == 0
+    assert abs(part[k * d + k] - d1.sum() * (n / 4096)) < 0.05 * part[k * d + k]
+    s.close()
