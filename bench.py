@@ -189,6 +189,7 @@ def main():
     ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
     ap.add_argument("--rows", type=int, default=0, help="override total rows (debugging only; marks the line invalid)")
     ap.add_argument("--path", default="auto", choices=["auto", "small", "simt", "tc"])
+    ap.add_argument("--param", action="append", default=[], help="tuning: ID=VALUE passed to kmc_set_param")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -238,6 +239,9 @@ def main():
     shard.bind_points(X)
     shard.set_centroids(C0)
     shard.enable_profile(True)
+    for kv in args.param:
+        pid, val = kv.split("=")
+        shard.set_param(int(pid), float(val))
     torch.cuda.synchronize(dev)
 
     def one_step():

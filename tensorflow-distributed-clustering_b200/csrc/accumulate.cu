@@ -16,7 +16,6 @@ namespace kmc {
 
 constexpr int kSegRows = 1024;        // rows of one cluster summed by one CTA
 constexpr int kScatterChunk = 16384;  // rows per CTA in the scatter pass
-constexpr int kSegPMax = 4;           // column passes per lane
 
 // ---- histogram --------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) hist_kernel(const int32_t* __restrict__ labels, int64_t n, int K,
@@ -132,12 +131,17 @@ template <> struct RowVec<1> {
     __device__ __forceinline__ void load(const float* p) { v[0] = ld_stream_f1(p); }
 };
 
-template <int VEC>
+// One CTA sums one run of <= kSegRows rows of one cluster.  Each warp owns a contiguous slice of the
+// run: it reads 32 permutation entries with one coalesced load, then keeps 8/P rows (512 B each at
+// D=128) in flight per lane group before folding them into fp32 accumulators -- the gather is
+// latency-bound, so bytes in flight per SM are what sets the bandwidth.
+template <int VEC, int P>
 __global__ void __launch_bounds__(256)
 segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict__ cent,
               const int32_t* __restrict__ perm, const unsigned int* __restrict__ offsets,
               const unsigned int* __restrict__ segoff, double* __restrict__ partials, int lpr_log2) {
-    __shared__ float red[8][32 * VEC * kSegPMax];
+    constexpr int U = 8 / P;                   // row groups in flight
+    __shared__ float red[8][32 * VEC * P];
     __shared__ double red_in[8];
     const unsigned int seg_total = segoff[K];
     const unsigned int b = blockIdx.x;
@@ -158,14 +162,16 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
     const int RPW = 32 >> lpr_log2;            // rows per warp step
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int cl = lane & (LPR - 1), sub = lane >> lpr_log2;
-    const int col0 = blockIdx.y * (LPR * VEC * kSegPMax);
+    const int col0 = blockIdx.y * (LPR * VEC * P);
 
-    float acc[kSegPMax][VEC], cen[kSegPMax][VEC];
-    bool on[kSegPMax];
+    float acc[P][VEC], cen[P][VEC];
+    bool on[P];
+    int64_t coff[P];
 #pragma unroll
-    for (int p = 0; p < kSegPMax; ++p) {
+    for (int p = 0; p < P; ++p) {
         const int col = col0 + (p * LPR + cl) * VEC;
         on[p] = col < D;
+        coff[p] = col;
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
             acc[p][e] = 0.f;
@@ -173,66 +179,62 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
         }
     }
     float inert = 0.f;
-    const int step = 8 * RPW;
-    int r = warp * RPW + sub;
-    // two rows in flight per lane
-    for (; r + step < nrows; r += 2 * step) {
-        const int64_t i0 = perm[row_b + r], i1 = perm[row_b + r + step];
-        RowVec<VEC> a[kSegPMax], c2[kSegPMax];
+    const int per_warp = (nrows + 7) >> 3;
+    const int wb = warp * per_warp;
+    const int we = min(nrows, wb + per_warp);
+    for (int base = wb; base < we; base += 32) {
+        const int cnt = min(32, we - base);
+        const int myidx = (lane < cnt) ? perm[row_b + base + lane] : -1;
+        const int nsteps = (cnt + RPW - 1) >> (5 - lpr_log2);
+        for (int s0 = 0; s0 < nsteps; s0 += U) {
+            RowVec<VEC> v[U][P];
+            bool ok[U];
 #pragma unroll
-        for (int p = 0; p < kSegPMax; ++p)
-            if (on[p]) {
-                const int col = col0 + (p * LPR + cl) * VEC;
-                a[p].load(x + i0 * D + col);
-                c2[p].load(x + i1 * D + col);
-            }
+            for (int u = 0; u < U; ++u) {
+                const int j = ((s0 + u) << (5 - lpr_log2)) + sub;
+                const int idx = __shfl_sync(0xffffffffu, myidx, j & 31);
+                ok[u] = (s0 + u < nsteps) && (j < cnt);
+                if (ok[u]) {
+                    const float* rowp = x + (int64_t)idx * D;
 #pragma unroll
-        for (int p = 0; p < kSegPMax; ++p)
-            if (on[p]) {
-#pragma unroll
-                for (int e = 0; e < VEC; ++e) {
-                    acc[p][e] += a[p].v[e];
-                    float t = a[p].v[e] - cen[p][e];
-                    inert = fmaf(t, t, inert);
-                    acc[p][e] += c2[p].v[e];
-                    t = c2[p].v[e] - cen[p][e];
-                    inert = fmaf(t, t, inert);
+                    for (int p = 0; p < P; ++p)
+                        if (on[p]) v[u][p].load(rowp + coff[p]);
                 }
             }
-    }
-    for (; r < nrows; r += step) {
-        const int64_t i0 = perm[row_b + r];
 #pragma unroll
-        for (int p = 0; p < kSegPMax; ++p)
-            if (on[p]) {
-                const int col = col0 + (p * LPR + cl) * VEC;
-                RowVec<VEC> a;
-                a.load(x + i0 * D + col);
+            for (int u = 0; u < U; ++u) {
+                if (ok[u]) {
 #pragma unroll
-                for (int e = 0; e < VEC; ++e) {
-                    acc[p][e] += a.v[e];
-                    const float t = a.v[e] - cen[p][e];
-                    inert = fmaf(t, t, inert);
+                    for (int p = 0; p < P; ++p)
+                        if (on[p]) {
+#pragma unroll
+                            for (int e = 0; e < VEC; ++e) {
+                                acc[p][e] += v[u][p].v[e];
+                                const float t = v[u][p].v[e] - cen[p][e];
+                                inert = fmaf(t, t, inert);
+                            }
+                        }
                 }
             }
+        }
     }
     // fold the RPW row-groups of a warp together
     for (int o = LPR; o < 32; o <<= 1) {
 #pragma unroll
-        for (int p = 0; p < kSegPMax; ++p)
+        for (int p = 0; p < P; ++p)
 #pragma unroll
             for (int e = 0; e < VEC; ++e) acc[p][e] += __shfl_xor_sync(0xffffffffu, acc[p][e], o);
     }
     if (sub == 0) {
 #pragma unroll
-        for (int p = 0; p < kSegPMax; ++p)
+        for (int p = 0; p < P; ++p)
 #pragma unroll
             for (int e = 0; e < VEC; ++e) red[warp][(p * LPR + cl) * VEC + e] = acc[p][e];
     }
     const double in_w = warp_sum((double)inert);
     if (lane == 0) red_in[warp] = in_w;
     __syncthreads();
-    const int ncols = LPR * VEC * kSegPMax;
+    const int ncols = LPR * VEC * P;
     for (int cidx = threadIdx.x; cidx < ncols; cidx += blockDim.x) {
         const int col = col0 + cidx;
         if (col < D) {
@@ -288,16 +290,22 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s) 
         const int vec = vec4 ? 4 : 1;
         int lpr_log2 = 0;
         while ((1 << lpr_log2) < 32 && (1 << lpr_log2) * vec < D) ++lpr_log2;
-        const int cols_per_block = (1 << lpr_log2) * vec * kSegPMax;
+        const int cols_per_pass = (1 << lpr_log2) * vec;
+        int passes = (D + cols_per_pass - 1) / cols_per_pass;
+        passes = passes >= 4 ? 4 : (passes >= 2 ? 2 : 1);
+        const int cols_per_block = cols_per_pass * passes;
         const unsigned gy = (unsigned)((D + cols_per_block - 1) / cols_per_block);
         const int64_t gx = (c->n + kSegRows - 1) / kSegRows + K;
         dim3 grid((unsigned)gx, gy);
-        if (vec4)
-            segsum_kernel<4><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), c->perm(), offsets, segoff,
-                                                  c->partials(), lpr_log2);
-        else
-            segsum_kernel<1><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), c->perm(), offsets, segoff,
-                                                  c->partials(), lpr_log2);
+#define KMC_SEGSUM(V, PP)                                                                                  \
+    segsum_kernel<V, PP><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), c->perm(), offsets, segoff, \
+                                              c->partials(), lpr_log2)
+        if (vec4) {
+            if (passes == 1) KMC_SEGSUM(4, 1); else if (passes == 2) KMC_SEGSUM(4, 2); else KMC_SEGSUM(4, 4);
+        } else {
+            if (passes == 1) KMC_SEGSUM(1, 1); else if (passes == 2) KMC_SEGSUM(1, 2); else KMC_SEGSUM(1, 4);
+        }
+#undef KMC_SEGSUM
         KMC_CUDA(cudaGetLastError());
     }
     c->launches += 4;

@@ -17,9 +17,10 @@
 // appended to a worklist and re-decided by the exact fp32 difference-form kernel
 // (assign_simt.cu), so the final labels equal an exact fp32 argmin with lowest-index ties.
 //
-// Warp roles (256 threads, one CTA per SM, persistent over 128-row tiles):
+// Warp roles (384 threads, one CTA per SM, persistent over 128-row tiles):
 //   warp 0  TMA producer      warp 1  MMA issuer (one thread)     warp 2  TMEM alloc/dealloc
-//   warps 4-7  epilogue: tcgen05.ld 32 lanes x 32 columns, running top-2 in registers
+//   warps 4-11  epilogue: tcgen05.ld 32 lanes x 32 columns, running top-2 in registers (two warps
+//   per TMEM lane quarter, each scanning one 128-column half of the accumulator tile)
 // Pipelines: A tiles (points, resident for the whole K sweep, double buffered when they fit),
 // B stages (centroid plane chunks, 3-4 deep ring), two TMEM accumulators of 256 columns.
 //
@@ -30,7 +31,7 @@
 
 namespace kmc {
 
-constexpr int kTcThreads = 256;
+constexpr int kTcThreads = 384;                     // 4 control warps + 8 epilogue warps
 constexpr uint32_t kTileBytesA = kTcBlockM * 128;   // 128 rows x 128 B  = 16 KB per (plane, chunk)
 constexpr uint32_t kStageBytesB = kTcBlockN * 128;  // 256 rows x 128 B  = 32 KB per stage
 constexpr uint32_t kTmemCols = 512;
@@ -38,6 +39,7 @@ constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kInstrDesc = (1u << 4) | ((uint32_t)(kTcBlockN >> 3) << 17) | ((uint32_t)(kTcBlockM >> 4) << 24);
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
+constexpr float kPackRel = 1.6e-5f;                 // > 2^-16: relative weight of the 7 packed index bits
 
 struct TcParams {
     int64_t n;
@@ -50,6 +52,7 @@ struct TcParams {
     int32_t* worklist;
     float* scores;       // debug: [n, K] or nullptr
     float gamma;
+    uint32_t pack_mask;  // 0xFFFFFF80, see pack_idx
 };
 
 template <int KC> struct TcCfg {
@@ -57,7 +60,7 @@ template <int KC> struct TcCfg {
     static constexpr uint32_t kABytes = kABufs * 2 * KC * kTileBytesA;
     static constexpr int kStages = (KC == 1) ? 4 : 3;
     static constexpr uint32_t kBBytes = kStages * kStageBytesB;
-    static constexpr uint32_t kCnOff = kABytes + kBBytes;             // 2 x 256 floats
+    static constexpr uint32_t kCnOff = kABytes + kBBytes;             // 2 x 256 floats (also the merge buffer)
     static constexpr uint32_t kBarOff = kCnOff + 2 * kTcBlockN * 4;   // mbarriers
     static constexpr uint32_t kSmemBytes = kBarOff + 256;
 };
@@ -85,40 +88,53 @@ __device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&r)[32]) {
                  :: "memory");
 }
 
+// Running best / second-best of one row.  The values carry the column index (within the warp's
+// 128-column half tile) in their 7 lowest mantissa bits, so the argmin needs no compare+select
+// per element: the min/max chain alone moves the index along.  The scores are offset per row by
+// S*|x|^2 (making them S*d >= 0, small for the best centroid), so the 2^-16 relative truncation
+// is far below the kernel's own error bound.
 struct Top2 {
     float m1, m2;
-    int a1;
 };
 
-// 32 accumulator columns of one row -> two running top-2 chains (even / odd columns).
+// `mask` (0xFFFFFF80) arrives as a kernel parameter on purpose: with two immediates the compiler
+// emits two LOP3 per element, with the mask in a register it is one (a & mask) | j.
+__device__ __forceinline__ float pack_idx(float v, int j, uint32_t mask) {
+    return __uint_as_float((__float_as_uint(v) & mask) | (uint32_t)j);
+}
+
+// two packed scores into a top-2 chain: 5 min/max ops (one of them 3-input) per 2 elements
+__device__ __forceinline__ void top2_pair(Top2& t, float p0, float p1) {
+    const float a = fminf(p0, p1), b = fmaxf(p0, p1);
+    const float u = fmaxf(t.m1, a);
+    t.m2 = fminf(fminf(t.m2, u), b);
+    t.m1 = fminf(t.m1, a);
+}
+
+// 32 accumulator columns of one row (column j0 + 0..31 of the warp's half tile)
 template <bool SCORES>
-__device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float* __restrict__ cn, int kbase,
-                                          Top2& e, Top2& o, float* __restrict__ score_row, int K, float inv_s) {
-    const float e_m1_in = e.m1, o_m1_in = o.m1;
-    int ej = 0, oj = 0;
+__device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float* __restrict__ cn, float off, int j0,
+                                          uint32_t mask, Top2& e, Top2& o, float* __restrict__ score_row, int kbase, int K,
+                                          float inv_s) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
         const float4 c4 = *reinterpret_cast<const float4*>(cn + 4 * q);
-        const float v0 = __uint_as_float(r[4 * q + 0]) + c4.x;
-        const float v1 = __uint_as_float(r[4 * q + 1]) + c4.y;
-        const float v2 = __uint_as_float(r[4 * q + 2]) + c4.z;
-        const float v3 = __uint_as_float(r[4 * q + 3]) + c4.w;
-        e.m2 = fminf(e.m2, fmaxf(e.m1, v0)); ej = (v0 < e.m1) ? (4 * q + 0) : ej; e.m1 = fminf(e.m1, v0);
-        o.m2 = fminf(o.m2, fmaxf(o.m1, v1)); oj = (v1 < o.m1) ? (4 * q + 1) : oj; o.m1 = fminf(o.m1, v1);
-        e.m2 = fminf(e.m2, fmaxf(e.m1, v2)); ej = (v2 < e.m1) ? (4 * q + 2) : ej; e.m1 = fminf(e.m1, v2);
-        o.m2 = fminf(o.m2, fmaxf(o.m1, v3)); oj = (v3 < o.m1) ? (4 * q + 3) : oj; o.m1 = fminf(o.m1, v3);
+        const float v0 = (__uint_as_float(r[4 * q + 0]) + c4.x) + off;
+        const float v1 = (__uint_as_float(r[4 * q + 1]) + c4.y) + off;
+        const float v2 = (__uint_as_float(r[4 * q + 2]) + c4.z) + off;
+        const float v3 = (__uint_as_float(r[4 * q + 3]) + c4.w) + off;
+        top2_pair(e, pack_idx(v0, j0 + 4 * q + 0, mask), pack_idx(v1, j0 + 4 * q + 1, mask));
+        top2_pair(o, pack_idx(v2, j0 + 4 * q + 2, mask), pack_idx(v3, j0 + 4 * q + 3, mask));
         if (SCORES && score_row) {
-            if (kbase + 4 * q + 0 < K) score_row[kbase + 4 * q + 0] = v0 * inv_s;
-            if (kbase + 4 * q + 1 < K) score_row[kbase + 4 * q + 1] = v1 * inv_s;
-            if (kbase + 4 * q + 2 < K) score_row[kbase + 4 * q + 2] = v2 * inv_s;
-            if (kbase + 4 * q + 3 < K) score_row[kbase + 4 * q + 3] = v3 * inv_s;
+            if (kbase + 4 * q + 0 < K) score_row[kbase + 4 * q + 0] = (v0 - off) * inv_s;
+            if (kbase + 4 * q + 1 < K) score_row[kbase + 4 * q + 1] = (v1 - off) * inv_s;
+            if (kbase + 4 * q + 2 < K) score_row[kbase + 4 * q + 2] = (v2 - off) * inv_s;
+            if (kbase + 4 * q + 3 < K) score_row[kbase + 4 * q + 3] = (v3 - off) * inv_s;
         }
     }
-    if (e.m1 < e_m1_in) e.a1 = kbase + ej;
-    if (o.m1 < o_m1_in) o.a1 = kbase + oj;
 }
 
-template <int KC, bool SCORES>
+template <int KC, bool SCORES, int NPASS>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const TcParams p) {
@@ -140,7 +156,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         if (smem_base & 1023u) { p.stats->watchdog = 0xA11u; __trap(); }
         for (int i = 0; i < 2; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); }
         for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), 4); }
+        for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), 8); }
         fence_barrier_init();
     }
     if (warp == 0 && lane == 0) {
@@ -167,9 +183,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 const int abuf = it % Cfg::kABufs;
                 const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) * kTcBlockM;
                 mbar_wait(a_empty(abuf), (((uint32_t)it / Cfg::kABufs) & 1u) ^ 1u, p.stats, 0x100u + abuf);
-                mbar_arrive_expect_tx(a_full(abuf), 2u * KC * kTileBytesA);
+                constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
+                mbar_arrive_expect_tx(a_full(abuf), (uint32_t)kPlanes * KC * kTileBytesA);
 #pragma unroll
-                for (int pl = 0; pl < 2; ++pl)
+                for (int pl = 0; pl < kPlanes; ++pl)
 #pragma unroll
                     for (int kc = 0; kc < KC; ++kc)
                         tma_load_2d_hint(smem_base + ((abuf * 2 + pl) * KC + kc) * kTileBytesA,
@@ -180,7 +197,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 for (int nt = 0; nt < p.n_ntiles; ++nt) {
                     for (int kc = 0; kc < KC; ++kc) {
 #pragma unroll
-                        for (int pl = 0; pl < 2; ++pl) {
+                        for (int pl = 0; pl < ((NPASS == 1) ? 1 : 2); ++pl) {
                             const int slot = sb % Cfg::kStages;
                             mbar_wait(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x200u + slot);
                             mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
@@ -222,12 +239,15 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                                      umma_desc_sw128(b_addr + k4 * 32), kInstrDesc, accum);
                             accum = 1;
                         }
+                        if (NPASS == 3) {
 #pragma unroll
-                        for (int k4 = 0; k4 < 4; ++k4)
-                            umma_f16(d_tmem, umma_desc_sw128(a_lo + kc * kTileBytesA + k4 * 32),
-                                     umma_desc_sw128(b_addr + k4 * 32), kInstrDesc, 1);
+                            for (int k4 = 0; k4 < 4; ++k4)
+                                umma_f16(d_tmem, umma_desc_sw128(a_lo + kc * kTileBytesA + k4 * 32),
+                                         umma_desc_sw128(b_addr + k4 * 32), kInstrDesc, 1);
+                        }
                         umma_commit(b_empty(slot));
                         ++sb;
+                        if (NPASS == 1) continue;
                         // stage with the centroid lo plane: x_hi*c_lo
                         slot = sb % Cfg::kStages;
                         mbar_wait(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x600u + slot);
@@ -247,8 +267,12 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         }
     } else if (warp >= 4) {
         // ===================== epilogue: running top-2 per row =====================
-        const int q = warp - 4;                         // TMEM lane quarter == warp_id % 4
-        const int et = threadIdx.x - 128;               // 0..127
+        // warps 4-7 scan columns 0..127 of every accumulator tile, warps 8-11 columns 128..255; both
+        // groups own the TMEM lane quarter (warp % 4).  Two warps per scheduler hide the TMEM-load
+        // and min/max-chain latencies of each other.
+        const int q = warp & 3;                         // TMEM lane quarter == warp_id % 4
+        const int half = (warp - 4) >> 2;               // which 128 columns of the 256-column tile
+        const int et = threadIdx.x - 128;               // 0..255
         float* cn_s = reinterpret_cast<float*>(smem + Cfg::kCnOff);
         const float sigma_x = p.stats->sigma_x, sigma_c = p.stats->sigma_c;
         const float inv_s = 1.f / (sigma_x * sigma_c);
@@ -257,46 +281,72 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         for (int it = 0; it < n_my_tiles; ++it) {
             const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * kTcBlockM + q * 32 + lane;
             const bool row_ok = row < p.n;
-            const float thr = row_ok ? 2.f * p.gamma * p.xnorm[row] * cmax : 0.f;
+            const float xn = row_ok ? p.xnorm[row] : 0.f;
+            const float thr = 2.f * p.gamma * xn * cmax;
+            const float off = xn * xn * (sigma_c / sigma_x);          // ~ S*|x|^2: scores become S*d >= 0
             float* score_row = (SCORES && p.scores && row_ok) ? p.scores + row * (int64_t)p.K : nullptr;
-            Top2 te = {INFINITY, INFINITY, 0}, to = {INFINITY, INFINITY, 0};
+            Top2 te = {INFINITY, INFINITY}, to = {INFINITY, INFINITY};
+            int a_e = 0, a_o = 0;
             for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                 const uint32_t buf = ac & 1u;
-                float* cn = cn_s + buf * kTcBlockN;
-                cn[et] = p.cnorm[nt * kTcBlockN + et];
-                cn[et + 128] = p.cnorm[nt * kTcBlockN + et + 128];
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                float* cw = cn_s + buf * kTcBlockN;
+                cw[et] = p.cnorm[nt * kTcBlockN + et];
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                const float* cn = cw + half * 128;
                 mbar_wait(t_full(buf), (ac >> 1) & 1u, p.stats, 0x700u + buf);
                 tc_fence_after_sync();
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kTcBlockN;
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kTcBlockN + half * 128;
+                const float e_in = te.m1, o_in = to.m1;
+                const int kbase = nt * kTcBlockN + half * 128;
                 uint32_t ra[32], rb[32];
                 tmem_ld_32x32(taddr, ra);
 #pragma unroll
-                for (int cc = 0; cc < kTcBlockN / 32; cc += 2) {
+                for (int cc = 0; cc < 4; cc += 2) {
                     tmem_ld_wait_dep(ra);
                     tmem_ld_32x32(taddr + (cc + 1) * 32, rb);
-                    epi_chunk<SCORES>(ra, cn + cc * 32, nt * kTcBlockN + cc * 32, te, to, score_row, p.K, inv_s);
+                    epi_chunk<SCORES>(ra, cn + cc * 32, off, cc * 32, p.pack_mask, te, to, score_row, kbase + cc * 32, p.K, inv_s);
                     tmem_ld_wait_dep(rb);
-                    if (cc + 2 < kTcBlockN / 32) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
-                    epi_chunk<SCORES>(rb, cn + (cc + 1) * 32, nt * kTcBlockN + (cc + 1) * 32, te, to, score_row, p.K, inv_s);
+                    if (cc + 2 < 4) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
+                    epi_chunk<SCORES>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32, p.pack_mask, te, to, score_row,
+                                      kbase + (cc + 1) * 32, p.K, inv_s);
                 }
                 tc_fence_before_sync();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(t_empty(buf));
+                // a changed best value carries its column in the low bits
+                if (__float_as_uint(te.m1) != __float_as_uint(e_in)) a_e = kbase + (int)(__float_as_uint(te.m1) & 0x7Fu);
+                if (__float_as_uint(to.m1) != __float_as_uint(o_in)) a_o = kbase + (int)(__float_as_uint(to.m1) & 0x7Fu);
             }
-            // merge the two chains
+            // merge the two chains of this thread ...
             float m1, m2;
             int a1;
-            if (to.m1 < te.m1 || (to.m1 == te.m1 && to.a1 < te.a1)) { m1 = to.m1; a1 = to.a1; m2 = fminf(te.m1, to.m2); }
-            else { m1 = te.m1; a1 = te.a1; m2 = fminf(to.m1, te.m2); }
-            if (row_ok) {
-                if (a1 >= p.K) a1 = 0;
-                p.labels[row] = a1;
-                if (p.worklist && (m2 - m1) <= thr) {
-                    const unsigned long long pos = atomicAdd(&p.stats->n_ambiguous, 1ull);
-                    p.worklist[pos] = (int32_t)row;
+            if (to.m1 < te.m1) { m1 = to.m1; a1 = a_o; m2 = fminf(te.m1, to.m2); }
+            else { m1 = te.m1; a1 = a_e; m2 = fminf(to.m1, te.m2); }
+            // ... and the two column halves of the row through shared memory (the bias buffer is idle here)
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            float* mg = cn_s;
+            if (half == 1) {
+                const int r = q * 32 + lane;
+                mg[r] = m1; mg[128 + r] = m2; mg[256 + r] = __int_as_float(a1);
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (half == 0) {
+                const int r = q * 32 + lane;
+                const float o1 = mg[r], o2 = mg[128 + r];
+                const int oa = __float_as_int(mg[256 + r]);
+                if (o1 < m1) { m2 = fminf(m1, o2); m1 = o1; a1 = oa; }
+                else { m2 = fminf(m2, o1); }
+                if (row_ok) {
+                    if (a1 >= p.K) a1 = 0;
+                    p.labels[row] = a1;
+                    const float pack_err = kPackRel * (fabsf(m1) + fabsf(m2));
+                    if (p.worklist && (m2 - m1) <= thr + pack_err) {
+                        const unsigned long long pos = atomicAdd(&p.stats->n_ambiguous, 1ull);
+                        p.worklist[pos] = (int32_t)row;
+                    }
                 }
             }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
         }
     }
 
@@ -348,7 +398,8 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
 template <int KC>
 static int launch_tc_kc(kmc_ctx* c, const TcParams& p, cudaStream_t s) {
     using Cfg = TcCfg<KC>;
-    auto kern = p.scores ? tc_assign_kernel<KC, true> : tc_assign_kernel<KC, false>;
+    auto kern = p.scores ? tc_assign_kernel<KC, true, 3>
+                         : (c->tc_passes == 1 ? tc_assign_kernel<KC, false, 1> : tc_assign_kernel<KC, false, 3>);
     KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes));
     const int grid = p.n_mtiles < c->sm_count ? p.n_mtiles : c->sm_count;
     kern<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, p);
@@ -373,6 +424,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, float* 
     p.worklist = worklist;
     p.scores = scores_out;
     p.gamma = (float)c->tc_gamma;
+    p.pack_mask = 0xFFFFFF80u;
     KMC_CUDA(cudaMemsetAsync(&c->stats()->n_ambiguous, 0, sizeof(unsigned long long), s));
     switch ((int)(c->D_pad / kTcChunkK)) {
         case 1: return launch_tc_kc<1>(c, p, s);

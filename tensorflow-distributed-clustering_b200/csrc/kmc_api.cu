@@ -43,6 +43,7 @@ static void layout_workspace(kmc_ctx* c) {
         c->off_xnorm = take(c->n * 4);
         c->off_cnorm = take(c->K_pad * 4);
         c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
+        c->off_ccdist = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;   // pruning table of the refine pass
         c->off_xhi = take(c->n * c->D_pad * 2);
         c->off_xlo = take(c->n * c->D_pad * 2);
     }
@@ -62,8 +63,15 @@ static int ensure_planes(kmc_ctx* c, cudaStream_t s) {
     if (c->path != KMC_PATH_TC || c->planes_ready) return 0;
     KMC_TRY(launch_centroid_absmax(c, s));
     KMC_TRY(launch_prep_centroids(c, s));
+    if (c->off_ccdist >= 0) KMC_TRY(launch_ccdist(c, s));
     c->planes_ready = true;
     return 0;
+}
+
+// exact re-decision of the rows in the worklist (c->perm()) left by the tensor kernel
+static int refine_worklist(kmc_ctx* c, int32_t* labels, cudaStream_t s) {
+    if (c->off_ccdist >= 0) return launch_refine(c, labels, s);
+    return launch_simt_assign(c, c->perm(), &c->stats()->n_ambiguous, 0, labels, s);
 }
 
 static int prof_mark(kmc_ctx* c, int slot, int which, cudaStream_t s) {
@@ -88,7 +96,7 @@ static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 0, s));    // after plane prep, before the tensor kernel
             KMC_TRY(launch_tc_assign(c, labels, c->perm(), nullptr, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
-            return launch_simt_assign(c, c->perm(), &c->stats()->n_ambiguous, 0, labels, s);
+            return refine_worklist(c, labels, s);
     }
     KMC_FAIL(KMC_E_INVALID, "bad kernel path %d", c->path);
 }
@@ -328,6 +336,7 @@ int kmc_update(kmc_ctx* c, void* stream) {
     KMC_TRY(launch_update(c, s));
     if (c->path == KMC_PATH_TC) {
         KMC_TRY(launch_prep_centroids(c, s));   // update_kernel refreshed c_absmax
+        if (c->off_ccdist >= 0) KMC_TRY(launch_ccdist(c, s));
         c->planes_ready = true;
     }
     KMC_TRY(prof_mark(c, slot, 5, s));
@@ -393,6 +402,9 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
         case KMC_PARAM_TC_GAMMA:
             if (!(value >= 0.0)) KMC_FAIL(KMC_E_INVALID, "gamma must be >= 0");
             c->tc_gamma = value;
+            return 0;
+        case 100:   /* undocumented timing experiment: number of MMA terms */
+            c->tc_passes = value == 1.0 ? 1 : 3;
             return 0;
         case KMC_PARAM_PROFILE:
             c->profile = value != 0.0;

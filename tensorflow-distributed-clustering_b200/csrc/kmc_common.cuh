@@ -64,6 +64,7 @@ struct kmc_ctx {
     // tensor-path geometry
     int64_t D_pad = 0, K_pad = 0;
     double tc_gamma = 0.0;
+    int tc_passes = 3;                  // experiment knob: MMA terms issued per score (1 = hi*hi only)
     // workspace
     char* ws = nullptr;
     int64_t ws_bytes = 0;
@@ -71,7 +72,7 @@ struct kmc_ctx {
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_perm = 0,
             off_hist = 0, off_offsets = 0, off_cursor = 0, off_segoff = 0,
             off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0,
-            off_sums_zero_bytes = 0;
+            off_ccdist = -1;
     const float* points = nullptr;
     bool have_centroids = false;
     bool planes_ready = false;
@@ -119,6 +120,9 @@ int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long 
 bool tc_path_supported(int64_t K, int64_t D);
 int tc_setup_tensor_maps(kmc_ctx* c);
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, float* scores_out, cudaStream_t s);
+// refine.cu
+int launch_ccdist(kmc_ctx* c, cudaStream_t s);
+int launch_refine(kmc_ctx* c, int32_t* labels, cudaStream_t s);
 // accumulate.cu
 int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s);
 // update.cu

@@ -1,0 +1,112 @@
+// Exact re-decision of the rows the tensor kernel could not certify (its two best approximate
+// scores are closer than its error bound).  One warp per row; candidates are pruned with the
+// triangle inequality before any exact distance is computed:
+//     |c_k - c_a| >= 2 |x - c_a|   ==>   |x - c_k| >= |x - c_a|      (a = the tensor kernel's pick)
+// so only centroids with ccdist[a][k] < 4 d(x, c_a) can win.  ccdist is the K x K matrix of squared
+// centroid distances, rebuilt once per iteration (K*K*D FMAs, negligible next to N*K*D).  The
+// surviving candidates get the reference's exact fp32 difference-form distance and a
+// lowest-index argmin, so the outcome equals a full exact scan.
+//
+// Part of the replacement of reference scripts/distribuitedClustering.py:221-234.
+#include "kmc_common.cuh"
+#include "kmc_device.cuh"
+
+namespace kmc {
+
+// ccdist[i][j] = sum_d (c_i[d] - c_j[d])^2, fp32, 16x16 output tile per CTA
+__global__ void __launch_bounds__(256) ccdist_kernel(const float* __restrict__ cent, int K, int D,
+                                                     float* __restrict__ cc) {
+    __shared__ float A[16][17], B[16][17];
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int i = blockIdx.y * 16 + ty, j = blockIdx.x * 16 + tx;
+    float acc = 0.f;
+    for (int d0 = 0; d0 < D; d0 += 16) {
+        const int ia = blockIdx.y * 16 + ty, ib = blockIdx.x * 16 + ty;
+        A[ty][tx] = (ia < K && d0 + tx < D) ? cent[(int64_t)ia * D + d0 + tx] : 0.f;
+        B[ty][tx] = (ib < K && d0 + tx < D) ? cent[(int64_t)ib * D + d0 + tx] : 0.f;
+        __syncthreads();
+#pragma unroll
+        for (int d = 0; d < 16; ++d) {
+            const float t = A[ty][d] - B[tx][d];
+            acc = fmaf(t, t, acc);
+        }
+        __syncthreads();
+    }
+    if (i < K && j < K) cc[(int64_t)i * K + j] = acc;
+}
+
+int launch_ccdist(kmc_ctx* c, cudaStream_t s) {
+    const int K = (int)c->K;
+    dim3 grid((K + 15) / 16, (K + 15) / 16);
+    ccdist_kernel<<<grid, 256, 0, s>>>(c->centroids(), K, (int)c->D, c->at<float>(c->off_ccdist));
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+template <int NPL>   // floats of the row held per lane: D <= 32 * NPL
+__global__ void __launch_bounds__(256)
+refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
+              const float* __restrict__ cc, const int32_t* __restrict__ worklist,
+              const unsigned long long* __restrict__ n_work_dev, int32_t* __restrict__ labels) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t n_work = (int64_t)(*n_work_dev);
+    for (int64_t w = warp; w < n_work; w += nwarps) {
+        const int64_t row = worklist[w];
+        const int a = labels[row];
+        float xr[NPL];
+#pragma unroll
+        for (int q = 0; q < NPL; ++q) {
+            const int d = lane + 32 * q;
+            xr[q] = d < D ? x[row * D + d] : 0.f;
+        }
+        auto dist_to = [&](int k) {
+            float acc = 0.f;
+#pragma unroll
+            for (int q = 0; q < NPL; ++q) {
+                const int d = lane + 32 * q;
+                const float t = xr[q] - (d < D ? cent[(int64_t)k * D + d] : 0.f);
+                acc = fmaf(t, t, acc);
+            }
+            return warp_sum(acc);
+        };
+        float best = dist_to(a);
+        int bk = a;
+        // a small relative margin absorbs the fp32 rounding of ccdist and of `best`
+        const float lim = 4.f * best * 1.0001f + 1e-30f;
+        const float* ccrow = cc + (int64_t)a * K;
+        for (int k0 = 0; k0 < K; k0 += 32) {
+            const int k = k0 + lane;
+            const bool cand = (k < K) && (k != a) && (ccrow[k] < lim);
+            unsigned m = __ballot_sync(0xffffffffu, cand);
+            while (m) {
+                const int kk = k0 + __ffs(m) - 1;
+                m &= m - 1;
+                const float d = dist_to(kk);
+                if (d < best || (d == best && kk < bk)) { best = d; bk = kk; }
+            }
+        }
+        if (lane == 0) labels[row] = bk;
+    }
+}
+
+int launch_refine(kmc_ctx* c, int32_t* labels, cudaStream_t s) {
+    const int blocks = c->sm_count * 8;
+    const int npl = (int)((c->D + 31) / 32);
+    const float* cc = c->at<float>(c->off_ccdist);
+    const unsigned long long* nw = &c->stats()->n_ambiguous;
+#define KMC_REFINE(N)                                                                                        \
+    refine_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, c->perm(), nw, labels)
+    if (npl <= 1) KMC_REFINE(1);
+    else if (npl <= 2) KMC_REFINE(2);
+    else if (npl <= 4) KMC_REFINE(4);
+    else KMC_REFINE(8);
+#undef KMC_REFINE
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+}  // namespace kmc

@@ -76,7 +76,7 @@ int launch_centroid_absmax(kmc_ctx* c, cudaStream_t s) {
 }
 
 // One warp per (padded) centroid row: C'_hi / C'_lo = split fp16 of (-2 * sigma_c * c), and
-// cn'[k] = sigma_x * sigma_c * |c_k|^2 (+inf for padding rows and NaN centroids, so they never
+// cn'[k] = sigma_x * sigma_c * |c_k|^2 (3e38 for padding rows and NaN centroids, so they never
 // win), plus max_k |C'_k| for the refine threshold.
 __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __restrict__ cent, int K, int D,
                                                              int K_pad, int D_pad, __half* __restrict__ chi,
@@ -106,7 +106,8 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
         ss = warp_sum(ss);
         ss_scaled = warp_sum(ss_scaled);
         float cn = (float)(ss * (double)sigma_x * (double)sigma_c);
-        // padding rows, NaN / infinite centroids: zero planes and an infinite norm -> never chosen
+        // padding rows, NaN / infinite centroids: zero planes and a huge (finite, so that the epilogue can
+        // pack an index into its low bits) bias -> never chosen
         const bool dead = (k >= K) || !(cn < INFINITY) || !(ss_scaled < INFINITY);
         for (int j = lane; j < D_pad; j += 32) {
             float v = 0.f;
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
             lr[j] = __float2half_rn(r);
         }
         if (lane == 0) {
-            cnorm[k] = dead ? INFINITY : cn;
+            cnorm[k] = dead ? 3.0e38f : cn;
             if (!dead) nmax = fmaxf(nmax, sqrtf(ss_scaled) * 1.001f);
         }
     }
