@@ -179,6 +179,32 @@ int kmc_get_phase_ms(kmc_ctx* ctx, float* out_ms, int n);
  */
 int kmc_debug_tc_scores(kmc_ctx* ctx, float* dev_scores, void* stream);
 
+/*
+ * Per-cluster sums, counts and inertia from labels the caller already has, WITHOUT any device
+ * allocation and without a kmc_ctx or workspace.  No counterpart in the reference.
+ *
+ * For hosts that are not allowed to call cudaMalloc: an operator a framework invokes with nothing
+ * but its input and output buffers (the framework's own pool owns all device memory and gives the
+ * operator no scratch), or a latency-critical serving loop on a fixed memory budget.  The scratch
+ * of the sorted accumulation (histogram, cursors, offsets, row permutation) lives in a fixed-size
+ * __device__ array inside the library instead, about 4.3 MB, which every GPU that loads the
+ * library holds until the process exits.  Limits: n_rows <= 1 048 576 and K <= 4096 per call;
+ * larger sizes are rejected with KMC_E_NOMEM (use a kmc_ctx with a caller-provided workspace).
+ *
+ *   dev_points    fp32 [n_rows, D] row-major          dev_labels  int32 [n_rows], values in [0, K)
+ *   dev_centroids fp32 [K, D] (for the inertia)       dev_partials double [K*D + K + 2], same layout
+ *                                                      as kmc_partials_ptr(); overwritten
+ *
+ * The first call on a device looks up the device address of that array (no allocation, but a
+ * runtime call), so make the first call on each device outside any stream capture.  All calls on
+ * one device share the array and it keeps the previous call's contents: the function clears what
+ * must start at zero, and two calls whose kernels overlap on the same GPU (different streams or
+ * threads) race on it -- serialise them.
+ */
+int kmc_cluster_sums_noalloc(int device, const float* dev_points, const int32_t* dev_labels,
+                             const float* dev_centroids, int64_t n_rows, int64_t D, int64_t K,
+                             double* dev_partials, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -47,6 +47,8 @@ SIGNATURES = {
     "kmc_set_param": (c_int, [c_void_p, c_int, c_double]),
     "kmc_get_phase_ms": (c_int, [c_void_p, POINTER(c_float), c_int]),
     "kmc_debug_tc_scores": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "kmc_cluster_sums_noalloc": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64,
+                                         c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -313,3 +313,117 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s) 
 }
 
 }  // namespace kmc
+
+// =================================================================================================
+// Allocation-free entry point (kmc_cluster_sums_noalloc, see include/kmc.h)
+//
+// Some hosts may not allocate device memory at all: an operator that a framework calls with only its
+// input and output buffers (the framework owns every byte of HBM through its own pool and hands the
+// operator no scratch), or a serving loop with a fixed memory budget where a cudaMalloc in the middle
+// of a request would synchronise the whole device or fail outright.  Those callers cannot follow the
+// kmc_workspace_bytes / kmc_bind_workspace protocol.  For them the scratch of the sorted accumulation
+// (histogram, cursors, offsets, segment offsets and the row permutation) lives in one file-scope
+// __device__ array of a fixed, modest size.  Every GPU that loads this library carries the array
+// until the process exits, every call on a device shares it, and it keeps whatever the previous call
+// left in it.
+// =================================================================================================
+namespace kmc {
+
+constexpr int64_t kNoAllocMaxRows = 1 << 20;     // rows per call
+constexpr int64_t kNoAllocMaxK = 4096;           // clusters per call
+constexpr int kNoAllocMaxDevices = 64;
+
+struct NoAllocScratch {
+    unsigned int hist[kNoAllocMaxK];             // hist and cursor are cleared together at the start of a call
+    unsigned int cursor[kNoAllocMaxK];
+    unsigned int offsets[kNoAllocMaxK + 64];
+    unsigned int segoff[kNoAllocMaxK + 64];
+    int32_t perm[kNoAllocMaxRows];
+};
+
+// In host code this name is only a handle for the runtime (cudaGetSymbolAddress below), never an address
+// a kernel could dereference; the kernels get the device address looked up once per device.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+static NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+static int g_noalloc_sms[kNoAllocMaxDevices] = {};
+
+// First call on a device: resolve the device address of the scratch array, with that device current.
+static int noalloc_setup(int device) {
+    if (g_noalloc_ptr[device]) return 0;
+    void* ptr = nullptr;
+    KMC_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+    int sms = 0;
+    KMC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    g_noalloc_sms[device] = sms;
+    g_noalloc_ptr[device] = static_cast<NoAllocScratch*>(ptr);
+    return 0;
+}
+
+}  // namespace kmc
+
+extern "C" int kmc_cluster_sums_noalloc(int device, const float* dev_points, const int32_t* dev_labels,
+                                        const float* dev_centroids, int64_t n_rows, int64_t D, int64_t K,
+                                        double* dev_partials, void* stream) {
+    using namespace kmc;
+    if (device < 0 || device >= kNoAllocMaxDevices) KMC_FAIL(KMC_E_INVALID, "device index %d out of range", device);
+    if (D < 1 || K < 1 || n_rows < 0) KMC_FAIL(KMC_E_INVALID, "need n_rows >= 0, D >= 1, K >= 1");
+    if (n_rows > kNoAllocMaxRows)
+        KMC_FAIL(KMC_E_NOMEM, "kmc_cluster_sums_noalloc handles at most %lld rows per call (got %lld): its scratch is "
+                 "a fixed-size device array; use a kmc_ctx with a caller-provided workspace for larger shards",
+                 (long long)kNoAllocMaxRows, (long long)n_rows);
+    if (K > kNoAllocMaxK)
+        KMC_FAIL(KMC_E_NOMEM, "kmc_cluster_sums_noalloc handles at most %lld clusters (got %lld)",
+                 (long long)kNoAllocMaxK, (long long)K);
+    if (K * D >= ((int64_t)1 << 31)) KMC_FAIL(KMC_E_INVALID, "K*D too large");
+    if (!dev_partials || (n_rows > 0 && (!dev_points || !dev_labels || !dev_centroids)))
+        KMC_FAIL(KMC_E_INVALID, "null argument");
+    KMC_CUDA(cudaSetDevice(device));
+    KMC_TRY(noalloc_setup(device));
+    NoAllocScratch* sc = g_noalloc_ptr[device];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int Ki = (int)K, Di = (int)D;
+
+    // the output accumulates through atomics and the histogram / cursors count up: all start at zero
+    KMC_CUDA(cudaMemsetAsync(dev_partials, 0, (size_t)(K * D + K + 2) * sizeof(double), s));
+    KMC_CUDA(cudaMemsetAsync(sc->hist, 0, 2 * sizeof(unsigned int) * (size_t)kNoAllocMaxK, s));
+    if (n_rows == 0) return 0;
+
+    {
+        int64_t blocks = (n_rows + 256 * 16 - 1) / (256 * 16);
+        const int64_t cap = (int64_t)g_noalloc_sms[device] * 8;
+        blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+        hist_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 4, s>>>(dev_labels, n_rows, Ki, sc->hist, 1);
+        KMC_CUDA(cudaGetLastError());
+    }
+    scan_kernel<<<1, 1024, 0, s>>>(sc->hist, Ki, sc->offsets, sc->segoff, dev_partials + K * D);
+    KMC_CUDA(cudaGetLastError());
+    {
+        const int64_t blocks = (n_rows + kScatterChunk - 1) / kScatterChunk;
+        scatter_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 8, s>>>(dev_labels, n_rows, Ki, sc->offsets, sc->cursor,
+                                                                    sc->perm, 1);
+        KMC_CUDA(cudaGetLastError());
+    }
+    {
+        const bool vec4 = (Di % 4 == 0) && ((reinterpret_cast<uintptr_t>(dev_points) & 15) == 0);
+        const int vec = vec4 ? 4 : 1;
+        int lpr_log2 = 0;
+        while ((1 << lpr_log2) < 32 && (1 << lpr_log2) * vec < Di) ++lpr_log2;
+        const int cols_per_pass = (1 << lpr_log2) * vec;
+        int passes = (Di + cols_per_pass - 1) / cols_per_pass;
+        passes = passes >= 4 ? 4 : (passes >= 2 ? 2 : 1);
+        const int cols_per_block = cols_per_pass * passes;
+        dim3 grid((unsigned)((n_rows + kSegRows - 1) / kSegRows + K), (unsigned)((Di + cols_per_block - 1) / cols_per_block));
+#define KMC_SEGSUM_NA(V, PP)                                                                                 \
+    segsum_kernel<V, PP><<<grid, 256, 0, s>>>(dev_points, Di, Ki, dev_centroids, sc->perm, sc->offsets, sc->segoff, \
+                                              dev_partials, lpr_log2)
+        if (vec4) {
+            if (passes == 1) KMC_SEGSUM_NA(4, 1); else if (passes == 2) KMC_SEGSUM_NA(4, 2); else KMC_SEGSUM_NA(4, 4);
+        } else {
+            if (passes == 1) KMC_SEGSUM_NA(1, 1); else if (passes == 2) KMC_SEGSUM_NA(1, 2); else KMC_SEGSUM_NA(1, 4);
+        }
+#undef KMC_SEGSUM_NA
+        KMC_CUDA(cudaGetLastError());
+    }
+    return 0;
+}
