@@ -316,7 +316,9 @@ def main():
                    "kernel_path": stats["path"], "seed": SEED, "parallelism": f"rows sharded over {world} GPU(s)",
                    "l2": "inputs (%.1f GB per GPU) exceed the 126 MB L2; no flush needed" % (n_local * D * 4 / 1e9)
                    if n_local * D * 4 > 4 * 126e6 else "inputs fit in L2: numbers are L2-resident",
-                   "refined_rows_last_step": stats["ambiguous"], "checks": checks},
+                   "refined_rows_last_step": stats["ambiguous"], "checks": checks,
+                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; 3-term split if >35% of rows need the refine)"
+                   if stats["path"] == "tc" else None},
         "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
     }
     if args.rows:

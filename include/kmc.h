@@ -155,6 +155,9 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
 /* Tunable parameters (advanced; defaults are chosen at kmc_create). */
 #define KMC_PARAM_TC_GAMMA  1   /* relative error bound of the split-fp16 tensor scores used to
                                    decide which rows go to the exact refine kernel */
+#define KMC_PARAM_TC_TERMS  3   /* tensor path: MMA terms per score. 1 = hi*hi only + exact refine of every
+                                   uncertified row; 3 = fp32-accurate split; 0 (default) = start with 1 where
+                                   that pays off and fall back to 3 if too many rows need the refine */
 #define KMC_PARAM_PROFILE   2   /* non-zero: record CUDA events around each phase (see below) */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 

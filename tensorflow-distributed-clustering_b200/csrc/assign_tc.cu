@@ -31,7 +31,6 @@
 
 namespace kmc {
 
-constexpr int kTcThreads = 384;                     // 4 control warps + 8 epilogue warps
 constexpr uint32_t kTileBytesA = kTcBlockM * 128;   // 128 rows x 128 B  = 16 KB per (plane, chunk)
 constexpr uint32_t kStageBytesB = kTcBlockN * 128;  // 256 rows x 128 B  = 32 KB per stage
 constexpr uint32_t kTmemCols = 512;
@@ -51,7 +50,8 @@ struct TcParams {
     int32_t* labels;
     int32_t* worklist;
     float* scores;       // debug: [n, K] or nullptr
-    float gamma;
+    float gamma;         // accumulate + split error of the 3-term score, relative to |X'||C'|
+    float gamma1;        // accumulate error of the 1-term score
     uint32_t pack_mask;  // 0xFFFFFF80, see pack_idx
 };
 
@@ -65,11 +65,17 @@ template <int KC> struct TcCfg {
     static constexpr uint32_t kSmemBytes = kBarOff + 256;
 };
 
+// Wait on an mbarrier phase.  The single-thread roles (producer, MMA issuer) share their scheduler
+// with epilogue warps, so a waiting thread backs off with nanosleep instead of spinning on the issue
+// slots the epilogue needs.  SLEEP_NS = 0 for the epilogue's own waits.
+template <unsigned SLEEP_NS>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, DeviceStats* st, unsigned code) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
+    unsigned spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > 6000000000LL) {       // ~3 s: a lost arrival; fail loudly instead of hanging
+        if (SLEEP_NS) __nanosleep(SLEEP_NS);
+        if ((++spins & 1023u) == 0 && clock64() - t0 > 6000000000LL) {   // ~3 s: fail loudly, do not hang
             st->watchdog = code;
             __threadfence_system();
             __trap();
@@ -112,17 +118,16 @@ __device__ __forceinline__ void top2_pair(Top2& t, float p0, float p1) {
 }
 
 // 32 accumulator columns of one row (column j0 + 0..31 of the warp's half tile)
-template <bool SCORES>
+template <bool SCORES, bool USE_OFF>
 __device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float* __restrict__ cn, float off, int j0,
                                           uint32_t mask, Top2& e, Top2& o, float* __restrict__ score_row, int kbase, int K,
                                           float inv_s) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
         const float4 c4 = *reinterpret_cast<const float4*>(cn + 4 * q);
-        const float v0 = (__uint_as_float(r[4 * q + 0]) + c4.x) + off;
-        const float v1 = (__uint_as_float(r[4 * q + 1]) + c4.y) + off;
-        const float v2 = (__uint_as_float(r[4 * q + 2]) + c4.z) + off;
-        const float v3 = (__uint_as_float(r[4 * q + 3]) + c4.w) + off;
+        float v0 = __uint_as_float(r[4 * q + 0]) + c4.x, v1 = __uint_as_float(r[4 * q + 1]) + c4.y;
+        float v2 = __uint_as_float(r[4 * q + 2]) + c4.z, v3 = __uint_as_float(r[4 * q + 3]) + c4.w;
+        if (USE_OFF) { v0 += off; v1 += off; v2 += off; v3 += off; }
         top2_pair(e, pack_idx(v0, j0 + 4 * q + 0, mask), pack_idx(v1, j0 + 4 * q + 1, mask));
         top2_pair(o, pack_idx(v2, j0 + 4 * q + 2, mask), pack_idx(v3, j0 + 4 * q + 3, mask));
         if (SCORES && score_row) {
@@ -134,8 +139,8 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float* 
     }
 }
 
-template <int KC, bool SCORES, int NPASS>
-__global__ void __launch_bounds__(kTcThreads, 1)
+template <int KC, bool SCORES, int NPASS, int EW>   // EW = epilogue warps (8 or 16)
+__global__ void __launch_bounds__(128 + 32 * EW, 1)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const TcParams p) {
     using Cfg = TcCfg<KC>;
@@ -156,7 +161,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         if (smem_base & 1023u) { p.stats->watchdog = 0xA11u; __trap(); }
         for (int i = 0; i < 2; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); }
         for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), 8); }
+        for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), EW); }
         fence_barrier_init();
     }
     if (warp == 0 && lane == 0) {
@@ -182,7 +187,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             auto load_a = [&](int it) {
                 const int abuf = it % Cfg::kABufs;
                 const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) * kTcBlockM;
-                mbar_wait(a_empty(abuf), (((uint32_t)it / Cfg::kABufs) & 1u) ^ 1u, p.stats, 0x100u + abuf);
+                mbar_wait<200>(a_empty(abuf), (((uint32_t)it / Cfg::kABufs) & 1u) ^ 1u, p.stats, 0x100u + abuf);
                 constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
                 mbar_arrive_expect_tx(a_full(abuf), (uint32_t)kPlanes * KC * kTileBytesA);
 #pragma unroll
@@ -199,7 +204,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
 #pragma unroll
                         for (int pl = 0; pl < ((NPASS == 1) ? 1 : 2); ++pl) {
                             const int slot = sb % Cfg::kStages;
-                            mbar_wait(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x200u + slot);
+                            mbar_wait<100>(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x200u + slot);
                             mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
                             tma_load_2d_hint(smem_base + Cfg::kABytes + slot * kStageBytesB, &tm_c, kc * kTcChunkK,
                                              pl * p.K_pad + nt * kTcBlockN, b_full(slot), kEvictLast);
@@ -218,19 +223,19 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             uint32_t sb = 0, ac = 0;
             for (int it = 0; it < n_my_tiles; ++it) {
                 const int abuf = it % Cfg::kABufs;
-                mbar_wait(a_full(abuf), ((uint32_t)it / Cfg::kABufs) & 1u, p.stats, 0x300u + abuf);
+                mbar_wait<40>(a_full(abuf), ((uint32_t)it / Cfg::kABufs) & 1u, p.stats, 0x300u + abuf);
                 const uint32_t a_hi = smem_base + (abuf * 2 + 0) * KC * kTileBytesA;
                 const uint32_t a_lo = smem_base + (abuf * 2 + 1) * KC * kTileBytesA;
                 for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                     const uint32_t buf = ac & 1u;
-                    mbar_wait(t_empty(buf), ((ac >> 1) & 1u) ^ 1u, p.stats, 0x400u + buf);
+                    mbar_wait<40>(t_empty(buf), ((ac >> 1) & 1u) ^ 1u, p.stats, 0x400u + buf);
                     tc_fence_after_sync();
                     const uint32_t d_tmem = tmem_base + buf * kTcBlockN;
                     uint32_t accum = 0;
                     for (int kc = 0; kc < KC; ++kc) {
                         // stage with the centroid hi plane: x_hi*c_hi, then x_lo*c_hi
                         int slot = sb % Cfg::kStages;
-                        mbar_wait(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x500u + slot);
+                        mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x500u + slot);
                         tc_fence_after_sync();
                         uint32_t b_addr = smem_base + Cfg::kABytes + slot * kStageBytesB;
 #pragma unroll
@@ -250,7 +255,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         if (NPASS == 1) continue;
                         // stage with the centroid lo plane: x_hi*c_lo
                         slot = sb % Cfg::kStages;
-                        mbar_wait(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x600u + slot);
+                        mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x600u + slot);
                         tc_fence_after_sync();
                         b_addr = smem_base + Cfg::kABytes + slot * kStageBytesB;
 #pragma unroll
@@ -270,44 +275,69 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         // warps 4-7 scan columns 0..127 of every accumulator tile, warps 8-11 columns 128..255; both
         // groups own the TMEM lane quarter (warp % 4).  Two warps per scheduler hide the TMEM-load
         // and min/max-chain latencies of each other.
+        constexpr int kGroups = EW / 4;                 // column groups of the 256-column tile
+        constexpr int kCols = kTcBlockN / kGroups;      // columns scanned per warp and tile (128 or 64)
+        constexpr int kEpiThreads = EW * 32;
         const int q = warp & 3;                         // TMEM lane quarter == warp_id % 4
-        const int half = (warp - 4) >> 2;               // which 128 columns of the 256-column tile
-        const int et = threadIdx.x - 128;               // 0..255
+        const int half = (warp - 4) >> 2;               // column group of this warp
+        const int et = threadIdx.x - 128;               // 0..kEpiThreads-1
         float* cn_s = reinterpret_cast<float*>(smem + Cfg::kCnOff);
         const float sigma_x = p.stats->sigma_x, sigma_c = p.stats->sigma_c;
         const float inv_s = 1.f / (sigma_x * sigma_c);
         const float cmax = __uint_as_float(p.stats->c_normmax_bits);
+        const float clomax = __uint_as_float(p.stats->c_lonormmax_bits);
         uint32_t ac = 0;
         for (int it = 0; it < n_my_tiles; ++it) {
             const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * kTcBlockM + q * 32 + lane;
             const bool row_ok = row < p.n;
-            const float xn = row_ok ? p.xnorm[row] : 0.f;
-            const float thr = 2.f * p.gamma * xn * cmax;
-            const float off = xn * xn * (sigma_c / sigma_x);          // ~ S*|x|^2: scores become S*d >= 0
+            float xn = 0.f, xlo = 0.f;
+            if (row_ok) {
+                const float2 nn = *reinterpret_cast<const float2*>(p.xnorm + 2 * row);
+                xn = nn.x; xlo = nn.y;
+            }
+            // certified if the two best scores are further apart than twice the score error bound:
+            // 3 terms: operand split + accumulator truncation; 1 term: the dropped x_lo.c and x.c_lo too
+            const float thr = (NPASS == 3) ? 2.f * p.gamma * xn * cmax
+                                           : 2.f * (xlo * cmax + xn * clomax + p.gamma1 * xn * cmax);
+            // 3 terms: offset by ~S*|x|^2 so that scores are S*d >= 0 and the index packing truncates
+            // 2^-16 of a SMALL number; with 1 term the threshold is far above that truncation anyway
+            const float off = (NPASS == 3) ? xn * xn * (sigma_c / sigma_x) : 0.f;
             float* score_row = (SCORES && p.scores && row_ok) ? p.scores + row * (int64_t)p.K : nullptr;
             Top2 te = {INFINITY, INFINITY}, to = {INFINITY, INFINITY};
             int a_e = 0, a_o = 0;
             for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                 const uint32_t buf = ac & 1u;
-                float* cw = cn_s + buf * kTcBlockN;
-                cw[et] = p.cnorm[nt * kTcBlockN + et];
-                asm volatile("bar.sync 1, 256;" ::: "memory");
-                const float* cn = cw + half * 128;
-                mbar_wait(t_full(buf), (ac >> 1) & 1u, p.stats, 0x700u + buf);
+                const float* cn;
+                if (NPASS == 1) {
+                    // the x_lo tile region is unused with one MMA term: every warp stages its own slice of
+                    // the biases there and needs no block-wide barrier per tile (warps drift apart freely)
+                    float* cw = reinterpret_cast<float*>(smem + KC * kTileBytesA) + (warp - 4) * kCols;
+                    if (lane < kCols / 4)
+                        *reinterpret_cast<float4*>(cw + 4 * lane) =
+                            *reinterpret_cast<const float4*>(p.cnorm + nt * kTcBlockN + half * kCols + 4 * lane);
+                    __syncwarp();
+                    cn = cw;
+                } else {
+                    float* cw = cn_s + buf * kTcBlockN;
+                    if (et < kTcBlockN) cw[et] = p.cnorm[nt * kTcBlockN + et];
+                    asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+                    cn = cw + half * kCols;
+                }
+                mbar_wait<0>(t_full(buf), (ac >> 1) & 1u, p.stats, 0x700u + buf);
                 tc_fence_after_sync();
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kTcBlockN + half * 128;
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kTcBlockN + half * kCols;
                 const float e_in = te.m1, o_in = to.m1;
-                const int kbase = nt * kTcBlockN + half * 128;
+                const int kbase = nt * kTcBlockN + half * kCols;
                 uint32_t ra[32], rb[32];
                 tmem_ld_32x32(taddr, ra);
 #pragma unroll
-                for (int cc = 0; cc < 4; cc += 2) {
+                for (int cc = 0; cc < kCols / 32; cc += 2) {
                     tmem_ld_wait_dep(ra);
                     tmem_ld_32x32(taddr + (cc + 1) * 32, rb);
-                    epi_chunk<SCORES>(ra, cn + cc * 32, off, cc * 32, p.pack_mask, te, to, score_row, kbase + cc * 32, p.K, inv_s);
+                    epi_chunk<SCORES, NPASS == 3>(ra, cn + cc * 32, off, cc * 32, p.pack_mask, te, to, score_row, kbase + cc * 32, p.K, inv_s);
                     tmem_ld_wait_dep(rb);
-                    if (cc + 2 < 4) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
-                    epi_chunk<SCORES>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32, p.pack_mask, te, to, score_row,
+                    if (cc + 2 < kCols / 32) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
+                    epi_chunk<SCORES, NPASS == 3>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32, p.pack_mask, te, to, score_row,
                                       kbase + (cc + 1) * 32, p.K, inv_s);
                 }
                 tc_fence_before_sync();
@@ -322,20 +352,25 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             int a1;
             if (to.m1 < te.m1) { m1 = to.m1; a1 = a_o; m2 = fminf(te.m1, to.m2); }
             else { m1 = te.m1; a1 = a_e; m2 = fminf(to.m1, te.m2); }
-            // ... and the two column halves of the row through shared memory (the bias buffer is idle here)
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            // ... and the column groups of the row through shared memory (the bias buffer is idle here)
             float* mg = cn_s;
-            if (half == 1) {
-                const int r = q * 32 + lane;
-                mg[r] = m1; mg[128 + r] = m2; mg[256 + r] = __int_as_float(a1);
+#pragma unroll
+            for (int g = 1; g < kGroups; ++g) {
+                asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+                if (half == g) {
+                    const int r = q * 32 + lane;
+                    mg[r] = m1; mg[128 + r] = m2; mg[256 + r] = __int_as_float(a1);
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+                if (half == 0) {
+                    const int r = q * 32 + lane;
+                    const float o1 = mg[r], o2 = mg[128 + r];
+                    const int oa = __float_as_int(mg[256 + r]);
+                    if (o1 < m1) { m2 = fminf(m1, o2); m1 = o1; a1 = oa; }
+                    else { m2 = fminf(m2, o1); }
+                }
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
             if (half == 0) {
-                const int r = q * 32 + lane;
-                const float o1 = mg[r], o2 = mg[128 + r];
-                const int oa = __float_as_int(mg[256 + r]);
-                if (o1 < m1) { m2 = fminf(m1, o2); m1 = o1; a1 = oa; }
-                else { m2 = fminf(m2, o1); }
                 if (row_ok) {
                     if (a1 >= p.K) a1 = 0;
                     p.labels[row] = a1;
@@ -346,7 +381,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     }
                 }
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
         }
     }
 
@@ -398,11 +433,12 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
 template <int KC>
 static int launch_tc_kc(kmc_ctx* c, const TcParams& p, cudaStream_t s) {
     using Cfg = TcCfg<KC>;
-    auto kern = p.scores ? tc_assign_kernel<KC, true, 3>
-                         : (c->tc_passes == 1 ? tc_assign_kernel<KC, false, 1> : tc_assign_kernel<KC, false, 3>);
+    auto kern = p.scores ? tc_assign_kernel<KC, true, 3, 8>
+                         : (c->tc_terms_now == 1 ? tc_assign_kernel<KC, false, 1, 8> : tc_assign_kernel<KC, false, 3, 8>);
+    const int threads = 128 + 32 * 8;
     KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes));
     const int grid = p.n_mtiles < c->sm_count ? p.n_mtiles : c->sm_count;
-    kern<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, p);
+    kern<<<grid, threads, Cfg::kSmemBytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, p);
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
@@ -424,6 +460,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, float* 
     p.worklist = worklist;
     p.scores = scores_out;
     p.gamma = (float)c->tc_gamma;
+    p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);
     p.pack_mask = 0xFFFFFF80u;
     KMC_CUDA(cudaMemsetAsync(&c->stats()->n_ambiguous, 0, sizeof(unsigned long long), s));
     switch ((int)(c->D_pad / kTcChunkK)) {

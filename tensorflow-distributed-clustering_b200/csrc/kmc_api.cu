@@ -4,6 +4,7 @@
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
 
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -40,10 +41,11 @@ static void layout_workspace(kmc_ctx* c) {
         c->off_perm = take(c->n * 4);
     }
     if (c->path == KMC_PATH_TC) {
-        c->off_xnorm = take(c->n * 4);
+        c->off_xnorm = take(c->n * 8);          // per row: |X'| and |X' - X'_hi|, both rounded up
         c->off_cnorm = take(c->K_pad * 4);
         c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
         c->off_ccdist = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;   // pruning table of the refine pass
+        c->off_nbr = (c->K <= 2048) ? take(c->K * c->K * 4) : -1;      // ... sorted nearest-first per centroid
         c->off_xhi = take(c->n * c->D_pad * 2);
         c->off_xlo = take(c->n * c->D_pad * 2);
     }
@@ -94,7 +96,19 @@ static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -
         case KMC_PATH_TC:
             KMC_TRY(ensure_planes(c, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 0, s));    // after plane prep, before the tensor kernel
+            // adaptive precision: if the last finished 1-term pass sent more than 35% of the rows to the
+            // exact refine kernel, the 3-term kernel (refines ~0.3%) is the cheaper way to the same labels
+            if (c->tc_terms == 0 && c->amb_pending && cudaEventQuery(c->amb_event) == cudaSuccess) {
+                c->amb_pending = false;
+                if (c->tc_terms_now == 1 && (double)*c->amb_host > 0.35 * (double)c->n) c->tc_terms_now = 3;
+            }
             KMC_TRY(launch_tc_assign(c, labels, c->perm(), nullptr, s));
+            if (c->tc_terms == 0 && !c->amb_pending) {
+                KMC_CUDA(cudaMemcpyAsync(c->amb_host, &c->stats()->n_ambiguous, sizeof(unsigned long long),
+                                         cudaMemcpyDeviceToHost, s));
+                KMC_CUDA(cudaEventRecord(c->amb_event, s));
+                c->amb_pending = true;
+            }
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
             return refine_worklist(c, labels, s);
     }
@@ -171,6 +185,19 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
         c->tc_gamma = 1.25 * (steps + 6.0) / 8388608.0;
     }
     layout_workspace(c);
+    if (path == KMC_PATH_TC) {
+        if (const char* e = getenv("KMC_TC_TERMS")) c->tc_terms = (e[0] == '1') ? 1 : (e[0] == '3' ? 3 : 0);
+        // one tensor term + exact refine wins when the 3-term kernel is MMA-bound (D_pad >= 128) and the
+        // refine pass has its sorted neighbour lists; the choice is revisited from the refine counts
+        c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->D_pad >= 128 && c->off_nbr >= 0) ? 1 : 3);
+        cudaError_t e1 = cudaHostAlloc(reinterpret_cast<void**>(&c->amb_host), sizeof(unsigned long long), cudaHostAllocDefault);
+        cudaError_t e2 = cudaEventCreateWithFlags(&c->amb_event, cudaEventDisableTiming);
+        if (e1 != cudaSuccess || e2 != cudaSuccess) {
+            kmc_destroy(c);
+            KMC_FAIL((int)(e1 != cudaSuccess ? e1 : e2), "could not create the pinned refine counter");
+        }
+        *c->amb_host = 0;
+    }
     *out = c;
     return 0;
 }
@@ -183,6 +210,8 @@ void kmc_destroy(kmc_ctx* c) {
         if (c->pinned_free[i]) cudaEventDestroy(c->pinned_free[i]);
         if (c->dev_stage[i]) cudaFree(c->dev_stage[i]);
     }
+    if (c->amb_host) cudaFreeHost(c->amb_host);
+    if (c->amb_event) cudaEventDestroy(c->amb_event);
     for (auto& ring : c->prof_ev)
         for (auto& e : ring)
             if (e) cudaEventDestroy(e);
@@ -403,8 +432,10 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             if (!(value >= 0.0)) KMC_FAIL(KMC_E_INVALID, "gamma must be >= 0");
             c->tc_gamma = value;
             return 0;
-        case 100:   /* undocumented timing experiment: number of MMA terms */
-            c->tc_passes = value == 1.0 ? 1 : 3;
+        case KMC_PARAM_TC_TERMS:
+            if (value != 0.0 && value != 1.0 && value != 3.0) KMC_FAIL(KMC_E_INVALID, "tensor terms must be 0, 1 or 3");
+            c->tc_terms = (int)value;
+            c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->D_pad >= 128 && c->off_nbr >= 0) ? 1 : 3);
             return 0;
         case KMC_PARAM_PROFILE:
             c->profile = value != 0.0;

@@ -50,7 +50,9 @@ struct DeviceStats {
     unsigned int watchdog;            // non-zero: a tensor-kernel barrier wait timed out
     float sigma_x;                    // power-of-two scale of the point planes
     float sigma_c;                    // power-of-two scale of the centroid planes (x -2 folded)
-    unsigned long long pad[2];
+    unsigned int c_lonormmax_bits;    // max_k |C' - C'_hi| (scaled units): bound for the 1-term kernel
+    unsigned int pad0;
+    unsigned long long pad1;
 };
 
 }  // namespace kmc
@@ -64,7 +66,11 @@ struct kmc_ctx {
     // tensor-path geometry
     int64_t D_pad = 0, K_pad = 0;
     double tc_gamma = 0.0;
-    int tc_passes = 3;                  // experiment knob: MMA terms issued per score (1 = hi*hi only)
+    int tc_terms = 0;                   // KMC_PARAM_TC_TERMS: 0 = adaptive, 1 or 3 = fixed
+    int tc_terms_now = 3;               // MMA terms of the next tensor pass
+    unsigned long long* amb_host = nullptr;   // pinned mirror of n_ambiguous of the last pass
+    cudaEvent_t amb_event = nullptr;
+    bool amb_pending = false;
     // workspace
     char* ws = nullptr;
     int64_t ws_bytes = 0;
@@ -72,7 +78,7 @@ struct kmc_ctx {
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_perm = 0,
             off_hist = 0, off_offsets = 0, off_cursor = 0, off_segoff = 0,
             off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0,
-            off_ccdist = -1;
+            off_ccdist = -1, off_nbr = -1;
     const float* points = nullptr;
     bool have_centroids = false;
     bool planes_ready = false;

@@ -35,19 +35,68 @@ __global__ void __launch_bounds__(256) ccdist_kernel(const float* __restrict__ c
     if (i < K && j < K) cc[(int64_t)i * K + j] = acc;
 }
 
+__global__ void nbrsort_kernel(float* __restrict__ cc, int32_t* __restrict__ nbr, int K);
+
 int launch_ccdist(kmc_ctx* c, cudaStream_t s) {
     const int K = (int)c->K;
     dim3 grid((K + 15) / 16, (K + 15) / 16);
     ccdist_kernel<<<grid, 256, 0, s>>>(c->centroids(), K, (int)c->D, c->at<float>(c->off_ccdist));
     KMC_CUDA(cudaGetLastError());
     c->launches++;
+    if (c->off_nbr >= 0) {
+        nbrsort_kernel<<<K, 512, 0, s>>>(c->at<float>(c->off_ccdist), c->at<int32_t>(c->off_nbr), K);
+        KMC_CUDA(cudaGetLastError());
+        c->launches++;
+    }
     return 0;
 }
 
-template <int NPL>   // floats of the row held per lane: D <= 32 * NPL
+// Sort every row of ccdist ascending (one CTA per row, bitonic sort of (distance, index) keys in
+// shared memory), in place, with the permutation in nbr: the refine kernel then walks the
+// neighbours of its anchor nearest-first and stops at the pruning radius, touching a few entries
+// instead of the whole row.  K <= kNbrSortMaxK.
+constexpr int kNbrSortMaxK = 2048;
+
+__global__ void __launch_bounds__(512) nbrsort_kernel(float* __restrict__ cc, int32_t* __restrict__ nbr, int K) {
+    __shared__ unsigned long long keys[kNbrSortMaxK];
+    const int a = blockIdx.x;
+    int P = 1;
+    while (P < K) P <<= 1;
+    for (int i = threadIdx.x; i < P; i += blockDim.x) {
+        unsigned long long key = ~0ull;
+        if (i < K) {
+            const float v = cc[(int64_t)a * K + i];
+            const unsigned int b = (v == v) ? __float_as_uint(fmaxf(v, 0.f)) : 0x7fffffffu;   // NaN last
+            key = ((unsigned long long)b << 32) | (unsigned int)i;
+        }
+        keys[i] = key;
+    }
+    __syncthreads();
+    for (int size = 2; size <= P; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
+                const int lo = 2 * t - (t & (stride - 1));
+                const int hi = lo + stride;
+                const bool up = ((lo & size) == 0);
+                const unsigned long long x0 = keys[lo], x1 = keys[hi];
+                if ((x0 > x1) == up) { keys[lo] = x1; keys[hi] = x0; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int i = threadIdx.x; i < K; i += blockDim.x) {
+        const unsigned long long key = keys[i];
+        const unsigned int b = (unsigned int)(key >> 32);
+        cc[(int64_t)a * K + i] = (b == 0x7fffffffu) ? __int_as_float(0x7fc00000) : __uint_as_float(b);
+        nbr[(int64_t)a * K + i] = (int32_t)(key & 0xffffffffu);
+    }
+}
+
+template <int NPL, bool SORTED>   // floats of the row held per lane: D <= 32 * NPL
 __global__ void __launch_bounds__(256)
 refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
-              const float* __restrict__ cc, const int32_t* __restrict__ worklist,
+              const float* __restrict__ cc, const int32_t* __restrict__ nbr,
+              const int32_t* __restrict__ worklist,
               const unsigned long long* __restrict__ n_work_dev, int32_t* __restrict__ labels) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -78,15 +127,20 @@ refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent
         const float lim = 4.f * best * 1.0001f + 1e-30f;
         const float* ccrow = cc + (int64_t)a * K;
         for (int k0 = 0; k0 < K; k0 += 32) {
-            const int k = k0 + lane;
-            const bool cand = (k < K) && (k != a) && (ccrow[k] < lim);
+            const int j = k0 + lane;
+            const float ccv = (j < K) ? ccrow[j] : INFINITY;
+            const int k = SORTED ? ((j < K) ? nbr[(int64_t)a * K + j] : -1) : j;
+            const bool cand = (j < K) && (k != a) && (ccv < lim);
             unsigned m = __ballot_sync(0xffffffffu, cand);
             while (m) {
-                const int kk = k0 + __ffs(m) - 1;
+                const int src = __ffs(m) - 1;
                 m &= m - 1;
+                const int kk = SORTED ? __shfl_sync(0xffffffffu, k, src) : (k0 + src);
                 const float d = dist_to(kk);
                 if (d < best || (d == best && kk < bk)) { best = d; bk = kk; }
             }
+            // sorted rows: once one entry is outside the pruning radius, all later ones are
+            if (SORTED && __ballot_sync(0xffffffffu, !(ccv < lim)) != 0u) break;
         }
         if (lane == 0) labels[row] = bk;
     }
@@ -97,8 +151,17 @@ int launch_refine(kmc_ctx* c, int32_t* labels, cudaStream_t s) {
     const int npl = (int)((c->D + 31) / 32);
     const float* cc = c->at<float>(c->off_ccdist);
     const unsigned long long* nw = &c->stats()->n_ambiguous;
-#define KMC_REFINE(N)                                                                                        \
-    refine_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, c->perm(), nw, labels)
+    const bool sorted = c->off_nbr >= 0;
+    const int32_t* nbr = sorted ? c->at<int32_t>(c->off_nbr) : nullptr;
+#define KMC_REFINE(N)                                                                                       \
+    do {                                                                                                    \
+        if (sorted)                                                                                         \
+            refine_kernel<N, true><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K,  \
+                                                         cc, nbr, c->perm(), nw, labels);                  \
+        else                                                                                                \
+            refine_kernel<N, false><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, \
+                                                          cc, nbr, c->perm(), nw, labels);                 \
+    } while (0)
     if (npl <= 1) KMC_REFINE(1);
     else if (npl <= 2) KMC_REFINE(2);
     else if (npl <= 4) KMC_REFINE(4);

@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) split_points_kernel(const float* __restri
         const float* xr = x + row * (int64_t)D;
         __half* hr = xhi + row * (int64_t)D_pad;
         __half* lr = xlo + row * (int64_t)D_pad;
-        float ss = 0.f;
+        float ss = 0.f, ss_lo = 0.f;
         for (int j = lane; j < D_pad; j += 32) {
             float v = (j < D) ? xr[j] * sigma : 0.f;
             __half h = __float2half_rn(v);
@@ -77,9 +77,14 @@ __global__ void __launch_bounds__(256) split_points_kernel(const float* __restri
             hr[j] = h;
             lr[j] = __float2half_rn(r);
             ss = fmaf(v, v, ss);
+            ss_lo = fmaf(r, r, ss_lo);
         }
         ss = warp_sum(ss);
-        if (lane == 0) xnorm[row] = sqrtf(ss) * 1.001f;
+        ss_lo = warp_sum(ss_lo);
+        if (lane == 0) {
+            xnorm[2 * row] = sqrtf(ss) * 1.001f;
+            xnorm[2 * row + 1] = sqrtf(ss_lo) * 1.001f;
+        }
     }
 }
 

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
-    float nmax = 0.f;
+    float nmax = 0.f, lomax = 0.f;
     for (int k = warp; k < K_pad; k += nwarps) {
         __half* hr = chi + (int64_t)k * D_pad;
         __half* lr = clo + (int64_t)k * D_pad;
@@ -109,6 +109,7 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
         // padding rows, NaN / infinite centroids: zero planes and a huge (finite, so that the epilogue can
         // pack an index into its low bits) bias -> never chosen
         const bool dead = (k >= K) || !(cn < INFINITY) || !(ss_scaled < INFINITY);
+        float ss_lo = 0.f;
         for (int j = lane; j < D_pad; j += 32) {
             float v = 0.f;
             if (!dead && j < D) v = -2.f * sigma_c * cent[(int64_t)k * D + j];
@@ -116,13 +117,19 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
             const float r = v - __half2float(h);
             hr[j] = h;
             lr[j] = __float2half_rn(r);
+            ss_lo = fmaf(r, r, ss_lo);
         }
+        ss_lo = warp_sum(ss_lo);
         if (lane == 0) {
             cnorm[k] = dead ? 3.0e38f : cn;
-            if (!dead) nmax = fmaxf(nmax, sqrtf(ss_scaled) * 1.001f);
+            if (!dead) {
+                nmax = fmaxf(nmax, sqrtf(ss_scaled) * 1.001f);
+                lomax = fmaxf(lomax, sqrtf(ss_lo) * 1.001f);
+            }
         }
     }
     if (lane == 0 && nmax > 0.f && nmax < INFINITY) atomicMax(&stats->c_normmax_bits, __float_as_uint(nmax));
+    if (lane == 0 && lomax > 0.f && lomax < INFINITY) atomicMax(&stats->c_lonormmax_bits, __float_as_uint(lomax));
 }
 
 int launch_prep_centroids(kmc_ctx* c, cudaStream_t s) {
@@ -130,6 +137,7 @@ int launch_prep_centroids(kmc_ctx* c, cudaStream_t s) {
     const int64_t cap = (int64_t)c->sm_count * 4;
     blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
     KMC_CUDA(cudaMemsetAsync(&c->stats()->c_normmax_bits, 0, sizeof(unsigned int), s));
+    KMC_CUDA(cudaMemsetAsync(&c->stats()->c_lonormmax_bits, 0, sizeof(unsigned int), s));
     __half* chi = c->at<__half>(c->off_cplanes);
     __half* clo = chi + c->K_pad * c->D_pad;
     prep_centroids_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), (int)c->K, (int)c->D, (int)c->K_pad,

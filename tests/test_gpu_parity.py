@@ -25,7 +25,7 @@ def _shard(pkg, X, K, device, path="auto", empty="keep"):
     return s
 
 
-def _check_iterations(pkg, X, C0, iters, device, path="auto", n_shards=1, form="diff", hist=None):
+def _check_iterations(pkg, X, C0, iters, device, path="auto", n_shards=1, form="diff", hist=None, tc_terms=None):
     """Run `iters` Lloyd iterations on the GPU, one C-ABI call per phase, checking every
     intermediate against the oracle (labels_t, counts_t, inertia_t vs C_t; C_{t+1})."""
     import torch
@@ -35,6 +35,8 @@ def _check_iterations(pkg, X, C0, iters, device, path="auto", n_shards=1, form="
     shards = [_shard(pkg, X[r0:r1], K, device, path) for r0, r1 in ranges]
     for s in shards:
         s.set_centroids(C0)
+        if tc_terms is not None:
+            s.set_param(pkg._lib.KMC_PARAM_TC_TERMS, tc_terms)
     C = np.asarray(C0, dtype=np.float64)
     for t in range(iters):
         ref = oracle.lloyd_iteration(X, C, n_shards=n_shards, form=form) if hist is None else None
@@ -97,6 +99,16 @@ def test_random_shapes_each_path(n, d, k, path, pkg, cuda_device):
     stats = _check_iterations(pkg, X, X[:k].copy(), 2, cuda_device, path=path,
                               form="gemm" if d * k > 20000 else "diff")
     assert stats["path"] == path
+
+
+@pytest.mark.parametrize("terms", [1, 3])
+@pytest.mark.parametrize("n,d,k", [(6000, 128, 1024), (5000, 64, 300), (3000, 256, 512), (2500, 32, 256)])
+def test_tensor_path_with_one_and_three_mma_terms(n, d, k, terms, pkg, cuda_device):
+    """Both precisions of the tensor kernel must end in the same exact labels: with one MMA term many
+    more rows go through the exact refine kernel, with three almost none."""
+    X, _ = pkg.datagen.blobs_numpy(n, d, max(2, k // 4), seed=n + d + k)      # several centroids per blob
+    stats = _check_iterations(pkg, X, X[:k].copy(), 2, cuda_device, path="tc", form="gemm", tc_terms=terms)
+    assert stats["path"] == "tc"
 
 
 def test_unscaled_data_ranges_on_tensor_path(pkg, cuda_device):
