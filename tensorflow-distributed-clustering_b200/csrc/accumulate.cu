@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(1024) scan_kernel(const unsigned int* __restri
         const unsigned int h = hist[i];
         offsets[i] = ro;
         segoff[i] = so;
-        counts_out[i] = (double)h;
+        counts_out[i] += (double)h;          // chunks of one pass add up (the buffer starts at zero)
         ro += h;
         so += (h + kSegRows - 1) / kSegRows;
     }
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(1024) scan_kernel(const unsigned int* __restri
 __global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict__ labels, int64_t n, int K,
                                                       const unsigned int* __restrict__ offsets,
                                                       unsigned int* __restrict__ cursor,
-                                                      int32_t* __restrict__ perm, int use_smem) {
+                                                      int32_t* __restrict__ perm, int use_smem, int64_t row_base) {
     extern __shared__ unsigned int sm[];
     unsigned int* lcnt = sm;        // [K] local counts, then local cursors
     unsigned int* lbase = sm + K;   // [K] global position of this CTA's first row of each cluster
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict_
     if (!use_smem) {
         for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
             const int l = labels[i];
-            if ((unsigned)l < (unsigned)K) perm[offsets[l] + atomicAdd(&cursor[l], 1u)] = (int32_t)i;
+            if ((unsigned)l < (unsigned)K) perm[offsets[l] + atomicAdd(&cursor[l], 1u)] = (int32_t)(row_base + i);
         }
         return;
     }
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict_
     __syncthreads();
     for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
         const int l = labels[i];
-        if ((unsigned)l < (unsigned)K) perm[lbase[l] + atomicAdd(&lcnt[l], 1u)] = (int32_t)i;
+        if ((unsigned)l < (unsigned)K) perm[lbase[l] + atomicAdd(&lcnt[l], 1u)] = (int32_t)(row_base + i);
     }
 }
 
@@ -252,24 +252,29 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
     }
 }
 
-int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s) {
+int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, int64_t r1, int chunk,
+                             cudaStream_t s) {
     const int K = (int)c->K, D = (int)c->D;
-    unsigned int* hist = c->at<unsigned int>(c->off_hist);
-    unsigned int* cursor = c->at<unsigned int>(c->off_cursor);
-    unsigned int* offsets = c->at<unsigned int>(c->off_offsets);
-    unsigned int* segoff = c->at<unsigned int>(c->off_segoff);
+    const int64_t n = r1 - r0;                       // rows of this chunk
+    if (n <= 0) return 0;
+    const int32_t* labels = labels_all + r0;
+    int32_t* perm = c->perm() + r0;                  // the chunk's own segment of the permutation
+    unsigned int* hist = c->sort_hist(chunk);
+    unsigned int* cursor = c->sort_cur(chunk);
+    unsigned int* offsets = c->sort_off(chunk);
+    unsigned int* segoff = c->sort_seg(chunk);
     // hist and cursor are adjacent in the workspace: one memset clears both
-    KMC_CUDA(cudaMemsetAsync(hist, 0, (size_t)(c->off_offsets - c->off_hist), s));
+    KMC_CUDA(cudaMemsetAsync(hist, 0, (size_t)c->sort_offsets, s));
 
     const int hist_smem_ok = (size_t)K * 4 <= 96 * 1024;
     {
-        int64_t blocks = (c->n + 256 * 16 - 1) / (256 * 16);
+        int64_t blocks = (n + 256 * 16 - 1) / (256 * 16);
         const int64_t cap = (int64_t)c->sm_count * 8;
         blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
         const size_t sm = hist_smem_ok ? (size_t)K * 4 : 0;
         if (sm > 48 * 1024)
             KMC_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        hist_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, c->n, K, hist, hist_smem_ok);
+        hist_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, n, K, hist, hist_smem_ok);
         KMC_CUDA(cudaGetLastError());
     }
     scan_kernel<<<1, 1024, 0, s>>>(hist, K, offsets, segoff, c->partials() + (int64_t)K * D);
@@ -277,11 +282,11 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s) 
     {
         const int sc_smem_ok = (size_t)K * 8 <= 192 * 1024;
         const size_t sm = sc_smem_ok ? (size_t)K * 8 : 0;
-        const int64_t blocks = (c->n + kScatterChunk - 1) / kScatterChunk;
+        const int64_t blocks = (n + kScatterChunk - 1) / kScatterChunk;
         if (sm > 48 * 1024)
             KMC_CUDA(cudaFuncSetAttribute(scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         if (blocks > 0) {
-            scatter_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, c->n, K, offsets, cursor, c->perm(), sc_smem_ok);
+            scatter_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, n, K, offsets, cursor, perm, sc_smem_ok, r0);
             KMC_CUDA(cudaGetLastError());
         }
     }
@@ -295,10 +300,10 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s) 
         passes = passes >= 4 ? 4 : (passes >= 2 ? 2 : 1);
         const int cols_per_block = cols_per_pass * passes;
         const unsigned gy = (unsigned)((D + cols_per_block - 1) / cols_per_block);
-        const int64_t gx = (c->n + kSegRows - 1) / kSegRows + K;
+        const int64_t gx = (n + kSegRows - 1) / kSegRows + K;
         dim3 grid((unsigned)gx, gy);
 #define KMC_SEGSUM(V, PP)                                                                                  \
-    segsum_kernel<V, PP><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), c->perm(), offsets, segoff, \
+    segsum_kernel<V, PP><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), perm, offsets, segoff, \
                                               c->partials(), lpr_log2)
         if (vec4) {
             if (passes == 1) KMC_SEGSUM(4, 1); else if (passes == 2) KMC_SEGSUM(4, 2); else KMC_SEGSUM(4, 4);
@@ -401,7 +406,7 @@ extern "C" int kmc_cluster_sums_noalloc(int device, const float* dev_points, con
     {
         const int64_t blocks = (n_rows + kScatterChunk - 1) / kScatterChunk;
         scatter_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 8, s>>>(dev_labels, n_rows, Ki, sc->offsets, sc->cursor,
-                                                                    sc->perm, 1);
+                                                                    sc->perm, 1, 0);
         KMC_CUDA(cudaGetLastError());
     }
     {

@@ -43,7 +43,9 @@ constexpr float kPackRel = 1.6e-5f;                 // > 2^-16: relative weight 
 struct TcParams {
     int64_t n;
     int K, K_pad;
-    int n_mtiles, n_ntiles;
+    int n_mtiles, n_ntiles;   // row tiles of this launch (starting at tile0), centroid tiles
+    int tile0;
+    unsigned long long* amb_counter;
     const float* xnorm;
     const float* cnorm;
     DeviceStats* stats;
@@ -55,13 +57,21 @@ struct TcParams {
     uint32_t pack_mask;  // 0xFFFFFF80, see pack_idx
 };
 
-template <int KC> struct TcCfg {
-    static constexpr int kABufs = (KC <= 2) ? 2 : 1;
-    static constexpr uint32_t kABytes = kABufs * 2 * KC * kTileBytesA;
-    static constexpr int kStages = (KC == 1) ? 4 : 3;
+// Shared-memory plan.  With one MMA term only the hi plane of the points is staged, which leaves
+// room on the SM for the CTAs of the accumulation kernels that run concurrently on the side stream.
+template <int KC, int NPASS> struct TcCfg {
+    static constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
+    static constexpr int kStages = (KC == 1 && NPASS == 3) ? 4 : 3;
     static constexpr uint32_t kBBytes = kStages * kStageBytesB;
-    static constexpr uint32_t kCnOff = kABytes + kBBytes;             // 2 x 256 floats (also the merge buffer)
-    static constexpr uint32_t kBarOff = kCnOff + 2 * kTcBlockN * 4;   // mbarriers
+    static constexpr uint32_t kOther = kBBytes + ((NPASS == 1) ? 8 * 128 * 4 : 2 * kTcBlockN * 4) + 256;
+    // the points tile is double buffered whenever two copies fit next to the B ring (227 KB per CTA)
+    static constexpr int kABufs = (2 * kPlanes * KC * kTileBytesA + kOther <= 232448u) ? 2 : 1;
+    static constexpr uint32_t kABytes = kABufs * kPlanes * KC * kTileBytesA;
+    static constexpr uint32_t kCnOff = kABytes + kBBytes;
+    // 3 terms: 2 x 256 bias floats staged per tile by the whole epilogue; 1 term: 128 floats per epilogue warp.
+    // Either region doubles as the buffer that merges the two column halves of a row (384 floats).
+    static constexpr uint32_t kCnBytes = (NPASS == 1) ? 8 * 128 * 4 : 2 * kTcBlockN * 4;
+    static constexpr uint32_t kBarOff = kCnOff + kCnBytes;            // mbarriers
     static constexpr uint32_t kSmemBytes = kBarOff + 256;
 };
 
@@ -143,7 +153,7 @@ template <int KC, bool SCORES, int NPASS, int EW>   // EW = epilogue warps (8 or
 __global__ void __launch_bounds__(128 + 32 * EW, 1)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const TcParams p) {
-    using Cfg = TcCfg<KC>;
+    using Cfg = TcCfg<KC, NPASS>;
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t smem_base = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -186,15 +196,14 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             uint32_t sb = 0;
             auto load_a = [&](int it) {
                 const int abuf = it % Cfg::kABufs;
-                const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) * kTcBlockM;
+                const int m0 = (p.tile0 + (int)blockIdx.x + it * (int)gridDim.x) * kTcBlockM;
                 mbar_wait<200>(a_empty(abuf), (((uint32_t)it / Cfg::kABufs) & 1u) ^ 1u, p.stats, 0x100u + abuf);
-                constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
-                mbar_arrive_expect_tx(a_full(abuf), (uint32_t)kPlanes * KC * kTileBytesA);
+                mbar_arrive_expect_tx(a_full(abuf), (uint32_t)Cfg::kPlanes * KC * kTileBytesA);
 #pragma unroll
-                for (int pl = 0; pl < kPlanes; ++pl)
+                for (int pl = 0; pl < Cfg::kPlanes; ++pl)
 #pragma unroll
                     for (int kc = 0; kc < KC; ++kc)
-                        tma_load_2d_hint(smem_base + ((abuf * 2 + pl) * KC + kc) * kTileBytesA,
+                        tma_load_2d_hint(smem_base + ((abuf * Cfg::kPlanes + pl) * KC + kc) * kTileBytesA,
                                          pl == 0 ? &tm_xhi : &tm_xlo, kc * kTcChunkK, m0, a_full(abuf), kEvictFirst);
             };
             load_a(0);
@@ -224,8 +233,8 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             for (int it = 0; it < n_my_tiles; ++it) {
                 const int abuf = it % Cfg::kABufs;
                 mbar_wait<40>(a_full(abuf), ((uint32_t)it / Cfg::kABufs) & 1u, p.stats, 0x300u + abuf);
-                const uint32_t a_hi = smem_base + (abuf * 2 + 0) * KC * kTileBytesA;
-                const uint32_t a_lo = smem_base + (abuf * 2 + 1) * KC * kTileBytesA;
+                const uint32_t a_hi = smem_base + (abuf * Cfg::kPlanes + 0) * KC * kTileBytesA;
+                const uint32_t a_lo = smem_base + (abuf * Cfg::kPlanes + (Cfg::kPlanes - 1)) * KC * kTileBytesA;
                 for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                     const uint32_t buf = ac & 1u;
                     mbar_wait<40>(t_empty(buf), ((ac >> 1) & 1u) ^ 1u, p.stats, 0x400u + buf);
@@ -288,7 +297,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         const float clomax = __uint_as_float(p.stats->c_lonormmax_bits);
         uint32_t ac = 0;
         for (int it = 0; it < n_my_tiles; ++it) {
-            const int64_t row = ((int64_t)blockIdx.x + (int64_t)it * gridDim.x) * kTcBlockM + q * 32 + lane;
+            const int64_t row = ((int64_t)p.tile0 + blockIdx.x + (int64_t)it * gridDim.x) * kTcBlockM + q * 32 + lane;
             const bool row_ok = row < p.n;
             float xn = 0.f, xlo = 0.f;
             if (row_ok) {
@@ -309,9 +318,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 const uint32_t buf = ac & 1u;
                 const float* cn;
                 if (NPASS == 1) {
-                    // the x_lo tile region is unused with one MMA term: every warp stages its own slice of
-                    // the biases there and needs no block-wide barrier per tile (warps drift apart freely)
-                    float* cw = reinterpret_cast<float*>(smem + KC * kTileBytesA) + (warp - 4) * kCols;
+                    // one MMA term: every warp stages its own slice of the biases and needs no block-wide
+                    // barrier per tile (the warps drift apart freely)
+                    float* cw = cn_s + (warp - 4) * kCols;
                     if (lane < kCols / 4)
                         *reinterpret_cast<float4*>(cw + 4 * lane) =
                             *reinterpret_cast<const float4*>(p.cnorm + nt * kTcBlockN + half * kCols + 4 * lane);
@@ -376,7 +385,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     p.labels[row] = a1;
                     const float pack_err = kPackRel * (fabsf(m1) + fabsf(m2));
                     if (p.worklist && (m2 - m1) <= thr + pack_err) {
-                        const unsigned long long pos = atomicAdd(&p.stats->n_ambiguous, 1ull);
+                        const unsigned long long pos = atomicAdd(p.amb_counter, 1ull);
                         p.worklist[pos] = (int32_t)row;
                     }
                 }
@@ -432,26 +441,30 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
 
 template <int KC>
 static int launch_tc_kc(kmc_ctx* c, const TcParams& p, cudaStream_t s) {
-    using Cfg = TcCfg<KC>;
     auto kern = p.scores ? tc_assign_kernel<KC, true, 3, 8>
                          : (c->tc_terms_now == 1 ? tc_assign_kernel<KC, false, 1, 8> : tc_assign_kernel<KC, false, 3, 8>);
     const int threads = 128 + 32 * 8;
-    KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes));
+    const uint32_t smem_bytes = (!p.scores && c->tc_terms_now == 1) ? TcCfg<KC, 1>::kSmemBytes : TcCfg<KC, 3>::kSmemBytes;
+    KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int grid = p.n_mtiles < c->sm_count ? p.n_mtiles : c->sm_count;
-    kern<<<grid, threads, Cfg::kSmemBytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, p);
+    kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, p);
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
 }
 
-int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, float* scores_out, cudaStream_t s) {
+int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
+                     float* scores_out, int64_t r0, int64_t r1, cudaStream_t s) {
     if (!c->tmaps_ready) KMC_FAIL(KMC_E_STATE, "tensor maps not built (bind workspace and points first)");
-    if (c->n <= 0) return 0;
+    if (r1 <= r0) return 0;
+    if (r0 % kTcBlockM) KMC_FAIL(KMC_E_INVALID, "row chunks of the tensor kernel start at multiples of %d", kTcBlockM);
     TcParams p;
-    p.n = c->n;
+    p.n = r1;
+    p.tile0 = (int)(r0 / kTcBlockM);
+    p.amb_counter = amb_counter;
     p.K = (int)c->K;
     p.K_pad = (int)c->K_pad;
-    p.n_mtiles = (int)((c->n + kTcBlockM - 1) / kTcBlockM);
+    p.n_mtiles = (int)((r1 - r0 + kTcBlockM - 1) / kTcBlockM);
     p.n_ntiles = (int)(c->K_pad / kTcBlockN);
     p.xnorm = c->at<float>(c->off_xnorm);
     p.cnorm = c->at<float>(c->off_cnorm);
@@ -462,7 +475,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, float* 
     p.gamma = (float)c->tc_gamma;
     p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);
     p.pack_mask = 0xFFFFFF80u;
-    KMC_CUDA(cudaMemsetAsync(&c->stats()->n_ambiguous, 0, sizeof(unsigned long long), s));
+    KMC_CUDA(cudaMemsetAsync(amb_counter, 0, sizeof(unsigned long long), s));
     switch ((int)(c->D_pad / kTcChunkK)) {
         case 1: return launch_tc_kc<1>(c, p, s);
         case 2: return launch_tc_kc<2>(c, p, s);

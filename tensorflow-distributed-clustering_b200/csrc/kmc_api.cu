@@ -33,10 +33,12 @@ static void layout_workspace(kmc_ctx* c) {
     c->off_centroids = take(c->K * c->D * 4);
     c->off_partials = take((c->K * c->D + c->K + 2) * 8);
     if (c->path != KMC_PATH_SMALL) {
-        c->off_hist = take(c->K * 4);
-        c->off_cursor = take(c->K * 4);
-        c->off_offsets = take((c->K + 1) * 4);
-        c->off_segoff = take((c->K + 1) * 4);
+        // counting-sort scratch, one block per row chunk: hist | cursor | offsets | segoff
+        c->sort_cursor = align256(c->K * 4);
+        c->sort_offsets = c->sort_cursor + align256(c->K * 4);
+        c->sort_segoff = c->sort_offsets + align256((c->K + 1) * 4);
+        c->sort_stride = c->sort_segoff + align256((c->K + 1) * 4);
+        c->off_sort = take(c->sort_stride * kMaxChunks);
         c->off_labels = take(c->n * 4);
         c->off_perm = take(c->n * 4);
     }
@@ -70,10 +72,30 @@ static int ensure_planes(kmc_ctx* c, cudaStream_t s) {
     return 0;
 }
 
-// exact re-decision of the rows in the worklist (c->perm()) left by the tensor kernel
-static int refine_worklist(kmc_ctx* c, int32_t* labels, cudaStream_t s) {
-    if (c->off_ccdist >= 0) return launch_refine(c, labels, s);
-    return launch_simt_assign(c, c->perm(), &c->stats()->n_ambiguous, 0, labels, s);
+// exact re-decision of the rows the tensor kernel left in `worklist` (their number is in *n_work)
+static int refine_worklist(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* n_work,
+                           cudaStream_t s) {
+    if (c->off_ccdist >= 0) return launch_refine(c, labels, worklist, n_work, s);
+    return launch_simt_assign(c, worklist, n_work, 0, labels, s);
+}
+
+// adaptive precision: if the last finished 1-term pass sent more than 35% of the rows to the exact
+// refine kernel, the 3-term kernel (refines ~0.3%) is the cheaper way to the same labels
+static void tc_policy_poll(kmc_ctx* c) {
+    if (c->tc_terms != 0 || !c->amb_pending || cudaEventQuery(c->amb_event) != cudaSuccess) return;
+    c->amb_pending = false;
+    unsigned long long total = 0;
+    for (int i = 0; i < kMaxChunks; ++i) total += c->amb_host[i];
+    if (c->tc_terms_now == 1 && (double)total > 0.35 * (double)c->n) c->tc_terms_now = 3;
+}
+
+static int tc_policy_post(kmc_ctx* c, cudaStream_t s) {
+    if (c->tc_terms != 0 || c->amb_pending) return 0;
+    KMC_CUDA(cudaMemcpyAsync(c->amb_host, c->stats()->n_amb, sizeof(unsigned long long) * kMaxChunks,
+                             cudaMemcpyDeviceToHost, s));
+    KMC_CUDA(cudaEventRecord(c->amb_event, s));
+    c->amb_pending = true;
+    return 0;
 }
 
 static int prof_mark(kmc_ctx* c, int slot, int which, cudaStream_t s) {
@@ -96,21 +118,12 @@ static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -
         case KMC_PATH_TC:
             KMC_TRY(ensure_planes(c, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 0, s));    // after plane prep, before the tensor kernel
-            // adaptive precision: if the last finished 1-term pass sent more than 35% of the rows to the
-            // exact refine kernel, the 3-term kernel (refines ~0.3%) is the cheaper way to the same labels
-            if (c->tc_terms == 0 && c->amb_pending && cudaEventQuery(c->amb_event) == cudaSuccess) {
-                c->amb_pending = false;
-                if (c->tc_terms_now == 1 && (double)*c->amb_host > 0.35 * (double)c->n) c->tc_terms_now = 3;
-            }
-            KMC_TRY(launch_tc_assign(c, labels, c->perm(), nullptr, s));
-            if (c->tc_terms == 0 && !c->amb_pending) {
-                KMC_CUDA(cudaMemcpyAsync(c->amb_host, &c->stats()->n_ambiguous, sizeof(unsigned long long),
-                                         cudaMemcpyDeviceToHost, s));
-                KMC_CUDA(cudaEventRecord(c->amb_event, s));
-                c->amb_pending = true;
-            }
+            tc_policy_poll(c);
+            KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
+            KMC_TRY(launch_tc_assign(c, labels, c->perm(), &c->stats()->n_amb[0], nullptr, 0, c->n, s));
+            KMC_TRY(tc_policy_post(c, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
-            return refine_worklist(c, labels, s);
+            return refine_worklist(c, labels, c->perm(), &c->stats()->n_amb[0], s);
     }
     KMC_FAIL(KMC_E_INVALID, "bad kernel path %d", c->path);
 }
@@ -190,13 +203,22 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
         // one tensor term + exact refine wins when the 3-term kernel is MMA-bound (D_pad >= 128) and the
         // refine pass has its sorted neighbour lists; the choice is revisited from the refine counts
         c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->D_pad >= 128 && c->off_nbr >= 0) ? 1 : 3);
-        cudaError_t e1 = cudaHostAlloc(reinterpret_cast<void**>(&c->amb_host), sizeof(unsigned long long), cudaHostAllocDefault);
+        cudaError_t e1 = cudaHostAlloc(reinterpret_cast<void**>(&c->amb_host), sizeof(unsigned long long) * kMaxChunks, cudaHostAllocDefault);
         cudaError_t e2 = cudaEventCreateWithFlags(&c->amb_event, cudaEventDisableTiming);
-        if (e1 != cudaSuccess || e2 != cudaSuccess) {
+        cudaError_t e3 = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking);
+        for (int i = 0; i < kMaxChunks && e3 == cudaSuccess; ++i)
+            e3 = cudaEventCreateWithFlags(&c->chunk_done[i], cudaEventDisableTiming);
+        if (e3 == cudaSuccess) e3 = cudaEventCreateWithFlags(&c->side_done, cudaEventDisableTiming);
+        if (e3 == cudaSuccess) e3 = cudaEventCreateWithFlags(&c->side_go, cudaEventDisableTiming);
+        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
             kmc_destroy(c);
-            KMC_FAIL((int)(e1 != cudaSuccess ? e1 : e2), "could not create the pinned refine counter");
+            KMC_FAIL((int)(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)), "could not create streams / events");
         }
-        *c->amb_host = 0;
+        for (int i = 0; i < kMaxChunks; ++i) c->amb_host[i] = 0;
+        // large shards: assign row chunk c+1 on the caller's stream while chunk c is refined and
+        // accumulated on the side stream (different bottlenecks: ALU/tensor pipe vs HBM)
+        c->n_chunks = (n_rows >= ((int64_t)1 << 22)) ? kMaxChunks : 1;
+        if (const char* e = getenv("KMC_CHUNKS")) { int v = atoi(e); c->n_chunks = v < 1 ? 1 : (v > kMaxChunks ? kMaxChunks : v); }
     }
     *out = c;
     return 0;
@@ -212,6 +234,11 @@ void kmc_destroy(kmc_ctx* c) {
     }
     if (c->amb_host) cudaFreeHost(c->amb_host);
     if (c->amb_event) cudaEventDestroy(c->amb_event);
+    if (c->side_stream) cudaStreamDestroy(c->side_stream);
+    for (auto& e : c->chunk_done)
+        if (e) cudaEventDestroy(e);
+    if (c->side_done) cudaEventDestroy(c->side_done);
+    if (c->side_go) cudaEventDestroy(c->side_go);
     for (auto& ring : c->prof_ev)
         for (auto& e : ring)
             if (e) cudaEventDestroy(e);
@@ -346,10 +373,44 @@ int kmc_accumulate(kmc_ctx* c, void* stream) {
         KMC_TRY(launch_small(c, true, nullptr, s));
         KMC_TRY(prof_mark(c, slot, 1, s));
         KMC_TRY(prof_mark(c, slot, 2, s));
+    } else if (c->path == KMC_PATH_TC && c->n_chunks > 1) {
+        // chunk-pipelined tensor path: the caller's stream runs the tensor kernel over one row chunk after
+        // the other; the side stream follows one chunk behind with the exact refine, the counting sort and
+        // the segmented sums of the finished chunk (its CTAs share the SMs with the persistent tensor CTAs)
+        KMC_TRY(ensure_planes(c, s));
+        KMC_TRY(prof_mark(c, slot, 0, s));
+        tc_policy_poll(c);
+        KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
+        KMC_CUDA(cudaEventRecord(c->side_go, s));                 // partials zeroed, centroid planes ready
+        KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->side_go, 0));
+        const int64_t tiles = (c->n + kTcBlockM - 1) / kTcBlockM;
+        const int64_t tiles_per_chunk = (tiles + c->n_chunks - 1) / c->n_chunks;
+        for (int ch = 0; ch < c->n_chunks; ++ch) {
+            const int64_t r0 = (int64_t)ch * tiles_per_chunk * kTcBlockM;
+            const int64_t r1 = (r0 + tiles_per_chunk * kTcBlockM < c->n) ? r0 + tiles_per_chunk * kTcBlockM : c->n;
+            if (r0 >= c->n) break;
+            KMC_TRY(launch_tc_assign(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[ch], nullptr, r0, r1, s));
+            static const bool refine_on_side = getenv("KMC_REFINE_MAIN") == nullptr;    // experiment knob
+            if (refine_on_side) {
+                KMC_CUDA(cudaEventRecord(c->chunk_done[ch], s));
+                KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->chunk_done[ch], 0));
+                KMC_TRY(refine_worklist(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[ch], c->side_stream));
+            } else {
+                KMC_TRY(refine_worklist(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[ch], s));
+                KMC_CUDA(cudaEventRecord(c->chunk_done[ch], s));
+                KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->chunk_done[ch], 0));
+            }
+            KMC_TRY(launch_sorted_accumulate(c, c->labels(), r0, r1, ch, c->side_stream));
+        }
+        KMC_TRY(prof_mark(c, slot, 1, s));                        // end of the last tensor kernel
+        KMC_TRY(prof_mark(c, slot, 2, s));
+        KMC_CUDA(cudaEventRecord(c->side_done, c->side_stream));
+        KMC_CUDA(cudaStreamWaitEvent(s, c->side_done, 0));        // phase "accumulate" = the exposed tail
+        KMC_TRY(tc_policy_post(c, s));
     } else {
         KMC_TRY(assign_into(c, c->labels(), s, slot));
         KMC_TRY(prof_mark(c, slot, 2, s));
-        KMC_TRY(launch_sorted_accumulate(c, c->labels(), s));
+        KMC_TRY(launch_sorted_accumulate(c, c->labels(), 0, c->n, 0, s));
     }
     KMC_TRY(prof_mark(c, slot, 3, s));
     if (c->profile) c->prof_acc_n++;
@@ -387,7 +448,9 @@ int kmc_read_stats(kmc_ctx* c, double* host_stats, void* stream) {
     for (int i = 0; i < KMC_STAT_COUNT; ++i) host_stats[i] = 0.0;
     host_stats[KMC_STAT_INERTIA] = inertia;
     host_stats[KMC_STAT_SHIFT2] = st.shift2;
-    host_stats[KMC_STAT_AMBIGUOUS] = (double)st.n_ambiguous;
+    unsigned long long amb = 0;
+    for (int i = 0; i < kMaxChunks; ++i) amb += st.n_amb[i];
+    host_stats[KMC_STAT_AMBIGUOUS] = (double)amb;
     host_stats[KMC_STAT_KERNEL_PATH] = (double)c->path;
     host_stats[KMC_STAT_LAUNCHES] = (double)c->launches;
     return 0;
@@ -482,7 +545,7 @@ int kmc_debug_tc_scores(kmc_ctx* c, float* dev_scores, void* stream) {
     KMC_CUDA(cudaSetDevice(c->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     KMC_TRY(ensure_planes(c, s));
-    return launch_tc_assign(c, c->labels(), nullptr, dev_scores, s);
+    return launch_tc_assign(c, c->labels(), nullptr, &c->stats()->n_amb[0], dev_scores, 0, c->n, s);
 }
 
 }  // extern "C"

@@ -38,12 +38,13 @@ constexpr int kTcBlockM = 128;   // rows per tensor tile (TMEM lanes)
 constexpr int kTcBlockN = 256;   // centroids per tensor tile (TMEM columns of one accumulator)
 constexpr int kTcChunkK = 64;    // fp16 elements per 128-byte swizzle row
 constexpr int kStatSlots = 16;
+constexpr int kMaxChunks = 4;    // row chunks of one accumulate pass (assign of chunk c+1 overlaps accumulate of chunk c)
 
 // Device-resident scalars written by kernels (all doubles / 64-bit so one memset clears them).
 struct DeviceStats {
     double inertia;        // last accumulate
     double shift2;         // last update
-    unsigned long long n_ambiguous;   // rows in the refine worklist (last tensor pass)
+    unsigned long long n_amb[kMaxChunks];   // rows in the refine worklist of each row chunk (last tensor pass)
     unsigned int x_absmax_bits;       // max |x| over the shard (fp32 bits), set at bind time
     unsigned int c_absmax_bits;       // max |c| after the last update / set_centroids
     unsigned int c_normmax_bits;      // max_k |C'_k| in scaled units (prep kernel)
@@ -52,7 +53,6 @@ struct DeviceStats {
     float sigma_c;                    // power-of-two scale of the centroid planes (x -2 folded)
     unsigned int c_lonormmax_bits;    // max_k |C' - C'_hi| (scaled units): bound for the 1-term kernel
     unsigned int pad0;
-    unsigned long long pad1;
 };
 
 }  // namespace kmc
@@ -68,7 +68,11 @@ struct kmc_ctx {
     double tc_gamma = 0.0;
     int tc_terms = 0;                   // KMC_PARAM_TC_TERMS: 0 = adaptive, 1 or 3 = fixed
     int tc_terms_now = 3;               // MMA terms of the next tensor pass
-    unsigned long long* amb_host = nullptr;   // pinned mirror of n_ambiguous of the last pass
+    unsigned long long* amb_host = nullptr;   // pinned mirror of the refine counts of the last pass [kMaxChunks]
+    int n_chunks = 1;                   // row chunks per accumulate pass (tensor path, large shards)
+    cudaStream_t side_stream = nullptr; // refine + accumulation of chunk c run here while chunk c+1 is assigned
+    cudaEvent_t chunk_done[kmc::kMaxChunks] = {};
+    cudaEvent_t side_done = nullptr, side_go = nullptr;
     cudaEvent_t amb_event = nullptr;
     bool amb_pending = false;
     // workspace
@@ -76,7 +80,7 @@ struct kmc_ctx {
     int64_t ws_bytes = 0;
     int64_t need_bytes = 0;
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_perm = 0,
-            off_hist = 0, off_offsets = 0, off_cursor = 0, off_segoff = 0,
+            off_sort = 0, sort_stride = 0, sort_cursor = 0, sort_offsets = 0, sort_segoff = 0,
             off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0,
             off_ccdist = -1, off_nbr = -1;
     const float* points = nullptr;
@@ -107,6 +111,11 @@ struct kmc_ctx {
     kmc::DeviceStats* stats() const { return at<kmc::DeviceStats>(off_stats); }
     int32_t* labels() const { return at<int32_t>(off_labels); }
     int32_t* perm() const { return at<int32_t>(off_perm); }
+    // per-chunk scratch of the counting sort: hist | cursor | offsets | segoff
+    unsigned int* sort_hist(int chunk) const { return at<unsigned int>(off_sort + chunk * sort_stride); }
+    unsigned int* sort_cur(int chunk) const { return at<unsigned int>(off_sort + chunk * sort_stride + sort_cursor); }
+    unsigned int* sort_off(int chunk) const { return at<unsigned int>(off_sort + chunk * sort_stride + sort_offsets); }
+    unsigned int* sort_seg(int chunk) const { return at<unsigned int>(off_sort + chunk * sort_stride + sort_segoff); }
 };
 
 namespace kmc {
@@ -125,12 +134,16 @@ int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long 
 // assign_tc.cu
 bool tc_path_supported(int64_t K, int64_t D);
 int tc_setup_tensor_maps(kmc_ctx* c);
-int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, float* scores_out, cudaStream_t s);
+// rows [r0, r1) (r0 a multiple of 128); uncertified rows are appended to `worklist`, counted in `amb_counter`
+int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
+                     float* scores_out, int64_t r0, int64_t r1, cudaStream_t s);
 // refine.cu
 int launch_ccdist(kmc_ctx* c, cudaStream_t s);
-int launch_refine(kmc_ctx* c, int32_t* labels, cudaStream_t s);
+int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* n_work_dev,
+                  cudaStream_t s);
 // accumulate.cu
-int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, cudaStream_t s);
+// sums / counts / inertia of rows [r0, r1), ADDED to the partial buffer; `chunk` selects the sort scratch
+int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, int64_t r0, int64_t r1, int chunk, cudaStream_t s);
 // update.cu
 int launch_update(kmc_ctx* c, cudaStream_t s);
 int launch_prep_centroids(kmc_ctx* c, cudaStream_t s);

@@ -146,21 +146,21 @@ refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent
     }
 }
 
-int launch_refine(kmc_ctx* c, int32_t* labels, cudaStream_t s) {
+int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* nw,
+                  cudaStream_t s) {
     const int blocks = c->sm_count * 8;
     const int npl = (int)((c->D + 31) / 32);
     const float* cc = c->at<float>(c->off_ccdist);
-    const unsigned long long* nw = &c->stats()->n_ambiguous;
     const bool sorted = c->off_nbr >= 0;
     const int32_t* nbr = sorted ? c->at<int32_t>(c->off_nbr) : nullptr;
 #define KMC_REFINE(N)                                                                                       \
     do {                                                                                                    \
         if (sorted)                                                                                         \
             refine_kernel<N, true><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K,  \
-                                                         cc, nbr, c->perm(), nw, labels);                  \
+                                                         cc, nbr, worklist, nw, labels);                  \
         else                                                                                                \
             refine_kernel<N, false><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, \
-                                                          cc, nbr, c->perm(), nw, labels);                 \
+                                                          cc, nbr, worklist, nw, labels);                 \
     } while (0)
     if (npl <= 1) KMC_REFINE(1);
     else if (npl <= 2) KMC_REFINE(2);

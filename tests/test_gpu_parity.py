@@ -111,6 +111,17 @@ def test_tensor_path_with_one_and_three_mma_terms(n, d, k, terms, pkg, cuda_devi
     assert stats["path"] == "tc"
 
 
+@pytest.mark.parametrize("chunks,terms", [(4, 1), (3, 3), (2, 0)])
+def test_chunk_pipelined_accumulate(chunks, terms, pkg, cuda_device, monkeypatch):
+    """Large shards are assigned chunk by chunk while the finished chunk is refined and accumulated on a
+    second stream; force that mode on a small shard and check every iteration against the oracle."""
+    monkeypatch.setenv("KMC_CHUNKS", str(chunks))
+    n, d, k = 50_000 + 77, 128, 512
+    X, _ = pkg.datagen.blobs_numpy(n, d, k // 4, seed=99)
+    stats = _check_iterations(pkg, X, X[:k].copy(), 3, cuda_device, path="tc", form="gemm", tc_terms=terms)
+    assert stats["path"] == "tc"
+
+
 def test_unscaled_data_ranges_on_tensor_path(pkg, cuda_device):
     # tiny and huge magnitudes go through the power-of-two scaling of the fp16 planes
     for scale in (1e-6, 3e4):
