@@ -63,14 +63,15 @@ template <int KC, int NPASS> struct TcCfg {
     static constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
     static constexpr int kStages = (KC == 1 && NPASS == 3) ? 4 : 3;
     static constexpr uint32_t kBBytes = kStages * kStageBytesB;
-    static constexpr uint32_t kOther = kBBytes + ((NPASS == 1) ? 8 * 128 * 4 : 2 * kTcBlockN * 4) + 256;
+    static constexpr uint32_t kOther = kBBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 256;
     // the points tile is double buffered whenever two copies fit next to the B ring (227 KB per CTA)
     static constexpr int kABufs = (2 * kPlanes * KC * kTileBytesA + kOther <= 232448u) ? 2 : 1;
     static constexpr uint32_t kABytes = kABufs * kPlanes * KC * kTileBytesA;
     static constexpr uint32_t kCnOff = kABytes + kBBytes;
     // 3 terms: 2 x 256 bias floats staged per tile by the whole epilogue; 1 term: 128 floats per epilogue warp.
     // Either region doubles as the buffer that merges the two column halves of a row (384 floats).
-    static constexpr uint32_t kCnBytes = (NPASS == 1) ? 8 * 128 * 4 : 2 * kTcBlockN * 4;
+    // (with 1 term the merge has its own 1536 bytes behind the per-warp slices, so it needs no block barrier)
+    static constexpr uint32_t kCnBytes = (NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4;
     static constexpr uint32_t kBarOff = kCnOff + kCnBytes;            // mbarriers
     static constexpr uint32_t kSmemBytes = kBarOff + 256;
 };
@@ -361,10 +362,23 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             int a1;
             if (to.m1 < te.m1) { m1 = to.m1; a1 = a_o; m2 = fminf(te.m1, to.m2); }
             else { m1 = te.m1; a1 = a_e; m2 = fminf(to.m1, te.m2); }
-            // ... and the column groups of the row through shared memory (the bias buffer is idle here)
-            float* mg = cn_s;
+            // ... and the column groups of the row through shared memory
+            if (NPASS == 1 && kGroups == 2) {
+                // only the two warps that share a TMEM lane quarter meet, on their own named barrier
+                float* mg = cn_s + 8 * 128 + q * 96;
+                if (half == 1) { mg[lane] = m1; mg[32 + lane] = m2; mg[64 + lane] = __int_as_float(a1); }
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+                if (half == 0) {
+                    const float o1 = mg[lane], o2 = mg[32 + lane];
+                    const int oa = __float_as_int(mg[64 + lane]);
+                    if (o1 < m1) { m2 = fminf(m1, o2); m1 = o1; a1 = oa; }
+                    else { m2 = fminf(m2, o1); }
+                }
+                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
+            }
+            float* mg = cn_s;                 // 3 terms: the bias buffer is idle here
 #pragma unroll
-            for (int g = 1; g < kGroups; ++g) {
+            for (int g = 1; g < ((NPASS == 1 && kGroups == 2) ? 1 : kGroups); ++g) {
                 asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
                 if (half == g) {
                     const int r = q * 32 + lane;
@@ -390,7 +404,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     }
                 }
             }
-            asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+            if (!(NPASS == 1 && kGroups == 2)) asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
         }
     }
 
