@@ -173,6 +173,20 @@ def run_reference_arm(args, cfg_name):
     }))
 
 
+def ncu_traffic_bytes(path, n_local, D, K):
+    """dram__bytes_read + dram__bytes_write of the dominant kernel per launch, from the committed ncu
+    capture (profiles/r1_traffic.json), scaled to the rows this rank's launch covers; None if the
+    capture is of another shape."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            t = json.load(f)["tc_assign_kernel"]
+        if path == "tc" and t["D"] == D and t["K"] == K:
+            return t["dram_bytes"] * (n_local / t["rows"])
+    except Exception:
+        pass
+    return None
+
+
 def workload_name(cfg_name):
     N, D, K, kind = CONFIGS[cfg_name]
     what = "synthetic 4K RGB image" if kind == "image" else "synthetic Gaussian blobs"
@@ -300,7 +314,7 @@ def main():
         roofline = {"bound": "hbm", "achieved": bytes_alg / t_assign / 1e9 if t_assign > 0 else None,
                     "peak": peaks["hbm_gbs"], "unit": "GB/s"}
     roofline["frac"] = (roofline["achieved"] / roofline["peak"]) if roofline["achieved"] else None
-    roofline["traffic"] = None          # dram bytes per launch come from the ncu capture under profiles/
+    roofline["traffic"] = ncu_traffic_bytes(stats["path"], n_local, D, K)
     roofline["peak_source"] = peaks["source"] + (" bf16 dense, sustained" if roofline["bound"] == "tensor" else " copy bandwidth")
     roofline["kernel"] = {"tc": "tc_assign_kernel", "small": "small_kernel", "simt": "simt_assign_kernel"}[stats["path"]]
     roofline["kernel_ms"] = phases["assign"]
@@ -317,7 +331,9 @@ def main():
                    "l2": "inputs (%.1f GB per GPU) exceed the 126 MB L2; no flush needed" % (n_local * D * 4 / 1e9)
                    if n_local * D * 4 > 4 * 126e6 else "inputs fit in L2: numbers are L2-resident",
                    "refined_rows_last_step": stats["ambiguous"], "checks": checks,
-                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; 3-term split if >35% of rows need the refine)"
+                   "iterations_timed": f"Lloyd iterations {args.warmup + 1}..{args.warmup + args.steps} of one run from C0 = X[0:K] "
+                                       "(the e2e leg times the whole run from iteration 1)",
+                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; 3-term split if >60% of rows need the refine)"
                    if stats["path"] == "tc" else None},
         "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
     }
@@ -325,14 +341,14 @@ def main():
         result["config"]["INVALID"] = "--rows override: not the BASELINE.json configuration"
 
     # ---- end to end through the public entry point, host buffers, copies inside the timed region ----
-    if not args.no_e2e and world == 1:
-        host, note = pinned_host_copy(X, N, D, K, dev)
+    if not args.no_e2e:
+        host, note = pinned_host_copy(X, n_local, D, K, dev)
         shard.close()
         del shard, X, part
         torch.cuda.empty_cache()
-        result["e2e"] = run_e2e(pkg, host, note, C0, D, K, args.steps, dev)
+        result["e2e"] = run_e2e(pkg, host, note, C0, D, K, args.steps, dev, world, N)
         del host
-    elif world > 1:
+    else:
         result["e2e"] = None
 
     # ---- CPU baseline: the oracle port on the host cores, bounded sample (rank 0, N = 1 only) ----
@@ -372,17 +388,35 @@ def pinned_host_copy(X_dev, N, D, K, dev):
     return host, note
 
 
-def run_e2e(pkg, host, note, C0, D, K, steps, dev):
-    """The same metric through the reference-facing entry point `distribuited_k_means`, points in
-    pinned HOST memory: the timed region holds the pinned H2D staging of every row, the one-time
-    split of the points, `steps` Lloyd iterations, and the D2H of the centroids and of the labels
-    (the reference's `cluster_idx`).  Bytes are per job divided by `steps`."""
+def run_e2e(pkg, host, note, C0, D, K, steps, dev, world, n_total):
+    """The same metric through the reference-facing entry point (`distribuited_k_means`; with one
+    process per GPU its SPMD form), points in pinned HOST memory: the timed region holds the pinned
+    H2D staging of every row, the one-time split of the points, `steps` Lloyd iterations (with the
+    NCCL all-reduce), and the D2H of the centroids and of the labels (the reference's `cluster_idx`).
+    Wall clock between barriers, max over ranks.  Bytes are per job and GPU divided by `steps`."""
+    import torch
+    import torch.distributed as dist
+
     rows = host.shape[0]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
-    res = pkg.distribuited_k_means(host, K, [f"/device:GPU:{dev.index}"], C0, steps)
+    if world > 1:
+        res = pkg.distribuited_k_means_spmd(host, K, C0, steps, device=dev)
+        dist.barrier()
+    else:
+        res = pkg.distribuited_k_means(host, K, [f"/device:GPU:{dev.index}"], C0, steps)
     dt = time.perf_counter() - t0
+    total_rows = rows
+    if world > 1:
+        t = torch.tensor([dt, float(rows)], dtype=torch.float64, device=dev)
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        dt, total_rows = float(tmax[0].item()), int(t[1].item())
     out = {
-        "value": rows * res["n_iter"] / dt, "unit": UNIT,
+        "value": total_rows * res["n_iter"] / dt, "unit": UNIT,
         "h2d_bytes_per_step": int(rows * D * 4 / max(steps, 1)),
         "d2h_bytes_per_step": int((K * D * 4 + rows * 4) / max(steps, 1)),
         "rows": rows, "iterations": res["n_iter"], "seconds": dt,

@@ -343,6 +343,56 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     }
 
 
+def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *, device=None, batch_size=None,
+                              tol=0.0, empty="keep", path="auto", return_labels=True, group=None):
+    """The same Lloyd loop with ONE PROCESS PER GPU (torchrun): every rank passes the rows the
+    reference's array_split rule (:184) gives it (`shard_ranges(N, world)[rank]`) and the same
+    initial centres; the per-GPU partial sums meet in one NCCL all-reduce per iteration
+    (`torch.distributed`, default group or `group`), replacing the reference's add_n on /cpu:0 (:257-258).
+    Returns the reference's result keys; `cluster_idx` holds this rank's labels only."""
+    torch = _torch()
+    import torch.distributed as dist
+
+    setup_ts = time.time()
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    device = torch.device(device)
+    rows = _as_host_matrix(local_rows)
+    n_local, D = int(rows.shape[0]), int(rows.shape[1])
+    init_center = np.array(initial_centers, dtype=np.float32, copy=True)
+    shard = LloydShard(n_local, D, int(K), device, empty=empty, path=path)
+    setup_time = float(time.time() - setup_ts)
+
+    initialization_ts = time.time()
+    if isinstance(rows, torch.Tensor) and rows.is_cuda:
+        shard.bind_points(rows.to(device=device, dtype=torch.float32).contiguous())
+    else:
+        shard.stage_from_host(rows, 0, batch_size)
+    shard.set_centroids(init_center)
+    torch.cuda.synchronize(device)
+    initialization_time = float(time.time() - initialization_ts)
+
+    aux_ts = time.time()
+    distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    reduce_fn = (lambda s: dist.all_reduce(s[0].partials, group=group)) if distributed else (lambda s: None)
+    n_iter, inertia, shift2 = lloyd_loop([shard], int(n_max_iters), tol, reduce_fn=reduce_fn)
+    torch.cuda.synchronize(device)
+    computation_time = float(time.time() - aux_ts)
+
+    end_center = shard.get_centroids()
+    labels = None
+    if return_labels:
+        labels = shard.assign().cpu().numpy().astype(np.int64)
+    shard.close()
+    return {
+        "end_center": end_center, "cluster_idx": labels, "centroids": labels, "init_center": init_center,
+        "setup_time": setup_time, "initialization_time": initialization_time,
+        "computation_time": computation_time, "n_iter": n_iter, "inertia": inertia,
+        "center_shift": float(np.sqrt(shift2)) if shift2 == shift2 else float("nan"),
+        "converged": bool(tol > 0.0 and shift2 <= tol),
+    }
+
+
 def run_experiments(batches, GPU_names, K, initial_centers, n_max_iters, func=None, **kwargs):
     """The reference's batch driver (:296-318): run ``func`` per batch, average the end centres
     across batches (``np.mean(result, axis=0)``, :310) and add up the three timers."""

@@ -79,14 +79,14 @@ static int refine_worklist(kmc_ctx* c, int32_t* labels, const int32_t* worklist,
     return launch_simt_assign(c, worklist, n_work, 0, labels, s);
 }
 
-// adaptive precision: if the last finished 1-term pass sent more than 35% of the rows to the exact
+// adaptive precision: if the last finished 1-term pass sent more than 60% of the rows to the exact
 // refine kernel, the 3-term kernel (refines ~0.3%) is the cheaper way to the same labels
 static void tc_policy_poll(kmc_ctx* c) {
     if (c->tc_terms != 0 || !c->amb_pending || cudaEventQuery(c->amb_event) != cudaSuccess) return;
     c->amb_pending = false;
     unsigned long long total = 0;
     for (int i = 0; i < kMaxChunks; ++i) total += c->amb_host[i];
-    if (c->tc_terms_now == 1 && (double)total > 0.35 * (double)c->n) c->tc_terms_now = 3;
+    if (c->tc_terms_now == 1 && (double)total > 0.60 * (double)c->n) c->tc_terms_now = 3;
 }
 
 static int tc_policy_post(kmc_ctx* c, cudaStream_t s) {
