@@ -333,7 +333,7 @@ def main():
                    "refined_rows_last_step": stats["ambiguous"], "checks": checks,
                    "iterations_timed": f"Lloyd iterations {args.warmup + 1}..{args.warmup + args.steps} of one run from C0 = X[0:K] "
                                        "(the e2e leg times the whole run from iteration 1)",
-                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; 3-term split if >60% of rows need the refine)"
+                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; device-side fallback to the 3-term split for chunks where >60% of the rows need the refine)"
                    if stats["path"] == "tc" else None},
         "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
     }

@@ -319,12 +319,15 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     cluster_idx = None
     last_labels = None
     if return_labels:
+        # labels leave the GPU already widened to the reference's int64, straight into one pinned array
         parts = [s.assign() for s in shards]
+        out = torch.empty(N, dtype=torch.int64, pin_memory=True)
+        for p, (r0, r1) in zip(parts, ranges):
+            out[r0:r1].copy_(p.to(torch.int64), non_blocking=True)
         for s in shards:
             torch.cuda.synchronize(s.device)
-        host_parts = [p.cpu().numpy().astype(np.int64) for p in parts]
-        cluster_idx = np.concatenate(host_parts) if host_parts else np.empty(0, np.int64)
-        last_labels = host_parts[-1]
+        cluster_idx = out.numpy()
+        last_labels = cluster_idx[ranges[-1][0]:ranges[-1][1]]
     for s in shards:
         s.close()
 
@@ -382,7 +385,10 @@ def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *,
     end_center = shard.get_centroids()
     labels = None
     if return_labels:
-        labels = shard.assign().cpu().numpy().astype(np.int64)
+        out = torch.empty(n_local, dtype=torch.int64, pin_memory=True)
+        out.copy_(shard.assign().to(torch.int64), non_blocking=True)
+        torch.cuda.synchronize(device)
+        labels = out.numpy()
     shard.close()
     return {
         "end_center": end_center, "cluster_idx": labels, "centroids": labels, "init_center": init_center,

@@ -46,6 +46,7 @@ struct TcParams {
     int n_mtiles, n_ntiles;   // row tiles of this launch (starting at tile0), centroid tiles
     int tile0;
     unsigned long long* amb_counter;
+    const unsigned int* gate_flag;   // null, or: run only if *gate_flag != 0 (device-side fallback to 3 terms)
     const float* xnorm;
     const float* cnorm;
     DeviceStats* stats;
@@ -155,6 +156,7 @@ __global__ void __launch_bounds__(128 + 32 * EW, 1)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const TcParams p) {
     using Cfg = TcCfg<KC, NPASS>;
+    if (p.gate_flag && *p.gate_flag == 0u) return;     // uniform for the whole grid
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t smem_base = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -453,12 +455,26 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
     return 0;
 }
 
+// Device-side decision between the two precisions: if the 1-term pass over a chunk left more than 60% of
+// its rows uncertified, raise the chunk's flag and restart its worklist; the 3-term kernel launched right
+// behind (gated on the flag) then redoes the chunk.  Keeps the stream fully asynchronous.
+__global__ void tc_gate_kernel(unsigned long long* amb_counter, unsigned int* flag, unsigned long long limit) {
+    if (*amb_counter > limit) { *flag = 1u; *amb_counter = 0ull; } else { *flag = 0u; }
+}
+
+int launch_tc_gate(kmc_ctx* c, unsigned long long* amb_counter, unsigned int* flag, int64_t rows, cudaStream_t s) {
+    tc_gate_kernel<<<1, 1, 0, s>>>(amb_counter, flag, (unsigned long long)(0.6 * (double)rows));
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
 template <int KC>
-static int launch_tc_kc(kmc_ctx* c, const TcParams& p, cudaStream_t s) {
+static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s) {
     auto kern = p.scores ? tc_assign_kernel<KC, true, 3, 8>
-                         : (c->tc_terms_now == 1 ? tc_assign_kernel<KC, false, 1, 8> : tc_assign_kernel<KC, false, 3, 8>);
+                         : (terms == 1 ? tc_assign_kernel<KC, false, 1, 8> : tc_assign_kernel<KC, false, 3, 8>);
     const int threads = 128 + 32 * 8;
-    const uint32_t smem_bytes = (!p.scores && c->tc_terms_now == 1) ? TcCfg<KC, 1>::kSmemBytes : TcCfg<KC, 3>::kSmemBytes;
+    const uint32_t smem_bytes = (!p.scores && terms == 1) ? TcCfg<KC, 1>::kSmemBytes : TcCfg<KC, 3>::kSmemBytes;
     KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int grid = p.n_mtiles < c->sm_count ? p.n_mtiles : c->sm_count;
     kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, p);
@@ -468,7 +484,8 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, cudaStream_t s) {
 }
 
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
-                     float* scores_out, int64_t r0, int64_t r1, cudaStream_t s) {
+                     float* scores_out, int64_t r0, int64_t r1, int terms, const unsigned int* gate_flag,
+                     cudaStream_t s) {
     if (!c->tmaps_ready) KMC_FAIL(KMC_E_STATE, "tensor maps not built (bind workspace and points first)");
     if (r1 <= r0) return 0;
     if (r0 % kTcBlockM) KMC_FAIL(KMC_E_INVALID, "row chunks of the tensor kernel start at multiples of %d", kTcBlockM);
@@ -476,6 +493,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.n = r1;
     p.tile0 = (int)(r0 / kTcBlockM);
     p.amb_counter = amb_counter;
+    p.gate_flag = gate_flag;
     p.K = (int)c->K;
     p.K_pad = (int)c->K_pad;
     p.n_mtiles = (int)((r1 - r0 + kTcBlockM - 1) / kTcBlockM);
@@ -489,12 +507,12 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.gamma = (float)c->tc_gamma;
     p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);
     p.pack_mask = 0xFFFFFF80u;
-    KMC_CUDA(cudaMemsetAsync(amb_counter, 0, sizeof(unsigned long long), s));
+    if (!gate_flag) KMC_CUDA(cudaMemsetAsync(amb_counter, 0, sizeof(unsigned long long), s));
     switch ((int)(c->D_pad / kTcChunkK)) {
-        case 1: return launch_tc_kc<1>(c, p, s);
-        case 2: return launch_tc_kc<2>(c, p, s);
-        case 4: return launch_tc_kc<4>(c, p, s);
-        case 3: return launch_tc_kc<4>(c, p, s);   // D_pad is rounded to 256 for 3 chunks at create time
+        case 1: return launch_tc_kc<1>(c, p, terms, s);
+        case 2: return launch_tc_kc<2>(c, p, terms, s);
+        case 4: return launch_tc_kc<4>(c, p, terms, s);
+        case 3: return launch_tc_kc<4>(c, p, terms, s);   // D_pad is rounded to 256 for 3 chunks at create time
         default: KMC_FAIL(KMC_E_UNSUPPORTED, "tensor path supports D <= 256 (D_pad=%lld)", (long long)c->D_pad);
     }
 }

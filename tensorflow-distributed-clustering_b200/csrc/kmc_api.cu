@@ -47,7 +47,7 @@ static void layout_workspace(kmc_ctx* c) {
         c->off_cnorm = take(c->K_pad * 4);
         c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
         c->off_ccdist = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;   // pruning table of the refine pass
-        c->off_nbr = (c->K <= 2048) ? take(c->K * c->K * 4) : -1;      // ... sorted nearest-first per centroid
+        c->off_nbr = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;      // ... sorted nearest-first per centroid
         c->off_xhi = take(c->n * c->D_pad * 2);
         c->off_xlo = take(c->n * c->D_pad * 2);
     }
@@ -79,19 +79,36 @@ static int refine_worklist(kmc_ctx* c, int32_t* labels, const int32_t* worklist,
     return launch_simt_assign(c, worklist, n_work, 0, labels, s);
 }
 
-// adaptive precision: if the last finished 1-term pass sent more than 60% of the rows to the exact
-// refine kernel, the 3-term kernel (refines ~0.3%) is the cheaper way to the same labels
+// adaptive precision, host side: once a finished pass is seen to have fallen back to 3 terms on the device
+// (more than 60% of a chunk uncertified), later passes start with 3 terms directly
+// One tensor pass over rows [r0, r1): with the adaptive policy a 1-term pass is followed by the on-device
+// gate and a gated 3-term pass, so poorly separated data cannot flood the exact refine kernel.
+static int tc_pass(kmc_ctx* c, int32_t* labels, int64_t r0, int64_t r1, int ch, cudaStream_t s) {
+    unsigned long long* cnt = &c->stats()->n_amb[ch];
+    KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, c->tc_terms_now, nullptr, s));
+    if (c->tc_terms == 0 && c->tc_terms_now == 1) {
+        unsigned int* flag = &c->stats()->tc3_flag[ch];
+        KMC_TRY(launch_tc_gate(c, cnt, flag, r1 - r0, s));
+        KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, 3, flag, s));
+    }
+    return 0;
+}
+
 static void tc_policy_poll(kmc_ctx* c) {
     if (c->tc_terms != 0 || !c->amb_pending || cudaEventQuery(c->amb_event) != cudaSuccess) return;
     c->amb_pending = false;
-    unsigned long long total = 0;
-    for (int i = 0; i < kMaxChunks; ++i) total += c->amb_host[i];
-    if (c->tc_terms_now == 1 && (double)total > 0.60 * (double)c->n) c->tc_terms_now = 3;
+    // amb_host: [kMaxChunks] refine counts, then [kMaxChunks] fallback flags (as 32-bit words)
+    const unsigned int* flags = reinterpret_cast<const unsigned int*>(c->amb_host + kMaxChunks);
+    bool fell_back = false;
+    for (int i = 0; i < kMaxChunks; ++i) fell_back |= flags[i] != 0u;
+    if (c->tc_terms_now == 1 && fell_back) c->tc_terms_now = 3;      // stop paying for the 1-term attempt
 }
 
 static int tc_policy_post(kmc_ctx* c, cudaStream_t s) {
     if (c->tc_terms != 0 || c->amb_pending) return 0;
     KMC_CUDA(cudaMemcpyAsync(c->amb_host, c->stats()->n_amb, sizeof(unsigned long long) * kMaxChunks,
+                             cudaMemcpyDeviceToHost, s));
+    KMC_CUDA(cudaMemcpyAsync(c->amb_host + kMaxChunks, c->stats()->tc3_flag, sizeof(unsigned int) * kMaxChunks,
                              cudaMemcpyDeviceToHost, s));
     KMC_CUDA(cudaEventRecord(c->amb_event, s));
     c->amb_pending = true;
@@ -120,7 +137,7 @@ static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 0, s));    // after plane prep, before the tensor kernel
             tc_policy_poll(c);
             KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
-            KMC_TRY(launch_tc_assign(c, labels, c->perm(), &c->stats()->n_amb[0], nullptr, 0, c->n, s));
+            KMC_TRY(tc_pass(c, labels, 0, c->n, 0, s));
             KMC_TRY(tc_policy_post(c, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
             return refine_worklist(c, labels, c->perm(), &c->stats()->n_amb[0], s);
@@ -200,10 +217,10 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
     layout_workspace(c);
     if (path == KMC_PATH_TC) {
         if (const char* e = getenv("KMC_TC_TERMS")) c->tc_terms = (e[0] == '1') ? 1 : (e[0] == '3' ? 3 : 0);
-        // one tensor term + exact refine wins when the 3-term kernel is MMA-bound (D_pad >= 128) and the
-        // refine pass has its sorted neighbour lists; the choice is revisited from the refine counts
-        c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->D_pad >= 128 && c->off_nbr >= 0) ? 1 : 3);
-        cudaError_t e1 = cudaHostAlloc(reinterpret_cast<void**>(&c->amb_host), sizeof(unsigned long long) * kMaxChunks, cudaHostAllocDefault);
+        // one tensor term + exact refine (fewer MMAs, less power, cheaper epilogue) whenever the refine pass
+        // has its sorted neighbour lists; the choice is revisited from the refine counts
+        c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->off_nbr >= 0) ? 1 : 3);
+        cudaError_t e1 = cudaHostAlloc(reinterpret_cast<void**>(&c->amb_host), sizeof(unsigned long long) * 2 * kMaxChunks, cudaHostAllocDefault);
         cudaError_t e2 = cudaEventCreateWithFlags(&c->amb_event, cudaEventDisableTiming);
         cudaError_t e3 = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking);
         for (int i = 0; i < kMaxChunks && e3 == cudaSuccess; ++i)
@@ -214,7 +231,7 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
             kmc_destroy(c);
             KMC_FAIL((int)(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)), "could not create streams / events");
         }
-        for (int i = 0; i < kMaxChunks; ++i) c->amb_host[i] = 0;
+        for (int i = 0; i < 2 * kMaxChunks; ++i) c->amb_host[i] = 0;
         // large shards: assign row chunk c+1 on the caller's stream while chunk c is refined and
         // accumulated on the side stream (different bottlenecks: ALU/tensor pipe vs HBM)
         c->n_chunks = (n_rows >= ((int64_t)1 << 22)) ? kMaxChunks : 1;
@@ -389,7 +406,7 @@ int kmc_accumulate(kmc_ctx* c, void* stream) {
             const int64_t r0 = (int64_t)ch * tiles_per_chunk * kTcBlockM;
             const int64_t r1 = (r0 + tiles_per_chunk * kTcBlockM < c->n) ? r0 + tiles_per_chunk * kTcBlockM : c->n;
             if (r0 >= c->n) break;
-            KMC_TRY(launch_tc_assign(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[ch], nullptr, r0, r1, s));
+            KMC_TRY(tc_pass(c, c->labels(), r0, r1, ch, s));
             static const bool refine_on_side = getenv("KMC_REFINE_MAIN") == nullptr;    // experiment knob
             if (refine_on_side) {
                 KMC_CUDA(cudaEventRecord(c->chunk_done[ch], s));
@@ -498,7 +515,7 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
         case KMC_PARAM_TC_TERMS:
             if (value != 0.0 && value != 1.0 && value != 3.0) KMC_FAIL(KMC_E_INVALID, "tensor terms must be 0, 1 or 3");
             c->tc_terms = (int)value;
-            c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->D_pad >= 128 && c->off_nbr >= 0) ? 1 : 3);
+            c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->off_nbr >= 0) ? 1 : 3);
             return 0;
         case KMC_PARAM_PROFILE:
             c->profile = value != 0.0;
@@ -545,7 +562,7 @@ int kmc_debug_tc_scores(kmc_ctx* c, float* dev_scores, void* stream) {
     KMC_CUDA(cudaSetDevice(c->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     KMC_TRY(ensure_planes(c, s));
-    return launch_tc_assign(c, c->labels(), nullptr, &c->stats()->n_amb[0], dev_scores, 0, c->n, s);
+    return launch_tc_assign(c, c->labels(), nullptr, &c->stats()->n_amb[0], dev_scores, 0, c->n, 3, nullptr, s);
 }
 
 }  // extern "C"

@@ -53,6 +53,7 @@ struct DeviceStats {
     float sigma_c;                    // power-of-two scale of the centroid planes (x -2 folded)
     unsigned int c_lonormmax_bits;    // max_k |C' - C'_hi| (scaled units): bound for the 1-term kernel
     unsigned int pad0;
+    unsigned int tc3_flag[kMaxChunks];      // set on the device when a 1-term pass certified too few rows of a chunk
 };
 
 }  // namespace kmc
@@ -135,8 +136,11 @@ int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long 
 bool tc_path_supported(int64_t K, int64_t D);
 int tc_setup_tensor_maps(kmc_ctx* c);
 // rows [r0, r1) (r0 a multiple of 128); uncertified rows are appended to `worklist`, counted in `amb_counter`
+// `terms` = 1 or 3 MMA terms; `gate_flag` (may be null): the launch is a no-op unless *gate_flag != 0
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
-                     float* scores_out, int64_t r0, int64_t r1, cudaStream_t s);
+                     float* scores_out, int64_t r0, int64_t r1, int terms, const unsigned int* gate_flag,
+                     cudaStream_t s);
+int launch_tc_gate(kmc_ctx* c, unsigned long long* amb_counter, unsigned int* flag, int64_t rows, cudaStream_t s);
 // refine.cu
 int launch_ccdist(kmc_ctx* c, cudaStream_t s);
 int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* n_work_dev,

@@ -44,7 +44,12 @@ int launch_ccdist(kmc_ctx* c, cudaStream_t s) {
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     if (c->off_nbr >= 0) {
-        nbrsort_kernel<<<K, 512, 0, s>>>(c->at<float>(c->off_ccdist), c->at<int32_t>(c->off_nbr), K);
+        int P = 1;
+        while (P < K) P <<= 1;
+        const size_t sm = (size_t)P * sizeof(unsigned long long);
+        if (sm > 48 * 1024)
+            KMC_CUDA(cudaFuncSetAttribute(nbrsort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        nbrsort_kernel<<<K, 512, sm, s>>>(c->at<float>(c->off_ccdist), c->at<int32_t>(c->off_nbr), K);
         KMC_CUDA(cudaGetLastError());
         c->launches++;
     }
@@ -54,11 +59,10 @@ int launch_ccdist(kmc_ctx* c, cudaStream_t s) {
 // Sort every row of ccdist ascending (one CTA per row, bitonic sort of (distance, index) keys in
 // shared memory), in place, with the permutation in nbr: the refine kernel then walks the
 // neighbours of its anchor nearest-first and stops at the pruning radius, touching a few entries
-// instead of the whole row.  K <= kNbrSortMaxK.
-constexpr int kNbrSortMaxK = 2048;
+// instead of the whole row.  K <= 8192 (64 KB of keys).
 
 __global__ void __launch_bounds__(512) nbrsort_kernel(float* __restrict__ cc, int32_t* __restrict__ nbr, int K) {
-    __shared__ unsigned long long keys[kNbrSortMaxK];
+    extern __shared__ unsigned long long keys[];
     const int a = blockIdx.x;
     int P = 1;
     while (P < K) P <<= 1;
@@ -146,6 +150,78 @@ refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent
     }
 }
 
+// Faster variant for sorted neighbour lists and D % 4 == 0: the warp evaluates FOUR candidates at a time
+// (8 lanes per candidate, each lane a strided set of float4 slices of the row), starting with the first
+// four entries of the anchor's list (entry 0 is the anchor itself), so the usual row -- anchor plus one
+// or two siblings inside the pruning radius -- costs one batch.
+template <int NV>   // float4 slices per lane: D <= 32 * NV * 4 / 4 ... lane t owns float4 indices t, t+8, ...
+__global__ void __launch_bounds__(256)
+refine4_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
+               const float* __restrict__ cc, const int32_t* __restrict__ nbr,
+               const int32_t* __restrict__ worklist, const unsigned long long* __restrict__ n_work_dev,
+               int32_t* __restrict__ labels) {
+    const int lane = threadIdx.x & 31, g = lane >> 3, t = lane & 7;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t n_work = (int64_t)(*n_work_dev);
+    const int nvec = D >> 2;
+    for (int64_t w = warp; w < n_work; w += nwarps) {
+        const int64_t row = worklist[w];
+        const int a = labels[row];
+        float4 xr[NV];
+        const float4* xp = reinterpret_cast<const float4*>(x + row * D);
+#pragma unroll
+        for (int q = 0; q < NV; ++q) {
+            const int v = t + 8 * q;
+            xr[q] = v < nvec ? xp[v] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const float* ccrow = cc + (int64_t)a * K;
+        const int32_t* nbrow = nbr + (int64_t)a * K;
+        float best = INFINITY, lim = INFINITY;
+        int bk = 0x7fffffff;
+        for (int j0 = 0; j0 < K; j0 += 4) {
+            const int j = j0 + g;
+            const float ccv = (j < K) ? ccrow[j] : INFINITY;
+            const int k = (j < K) ? nbrow[j] : -1;
+            float acc = 0.f;
+            if (k >= 0) {
+                const float4* cp = reinterpret_cast<const float4*>(cent + (int64_t)k * D);
+#pragma unroll
+                for (int q = 0; q < NV; ++q) {
+                    const int v = t + 8 * q;
+                    if (v < nvec) {
+                        const float4 cv = cp[v];
+                        float d0 = xr[q].x - cv.x, d1 = xr[q].y - cv.y, d2 = xr[q].z - cv.z, d3 = xr[q].w - cv.w;
+                        acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+                    }
+                }
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            if (j0 == 0) {
+                // entry 0 of the sorted list is the anchor (or an identical centroid): its distance sets the
+                // pruning radius; a small relative margin absorbs the fp32 rounding of ccdist and of the distance
+                const float d_anchor = __shfl_sync(0xffffffffu, acc, 0);
+                lim = 4.f * d_anchor * 1.0001f + 1e-30f;
+            }
+            float d = (k >= 0 && (ccv < lim || j == 0)) ? acc : INFINITY;
+            int kk = (d < INFINITY) ? k : 0x7fffffff;
+            // lexicographic (distance, index) min over the four candidate groups
+#pragma unroll
+            for (int o = 8; o <= 16; o <<= 1) {
+                const float od = __shfl_xor_sync(0xffffffffu, d, o);
+                const int ok = __shfl_xor_sync(0xffffffffu, kk, o);
+                if (od < d || (od == d && ok < kk)) { d = od; kk = ok; }
+            }
+            if (d < best || (d == best && kk < bk)) { best = d; bk = kk; }
+            // sorted: once an entry of this batch is outside the radius, all later ones are
+            if (__ballot_sync(0xffffffffu, !(ccv < lim)) != 0u) break;
+        }
+        if (lane == 0) labels[row] = (bk == 0x7fffffff) ? a : bk;
+    }
+}
+
 int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* nw,
                   cudaStream_t s) {
     const int blocks = c->sm_count * 8;
@@ -153,6 +229,20 @@ int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const un
     const float* cc = c->at<float>(c->off_ccdist);
     const bool sorted = c->off_nbr >= 0;
     const int32_t* nbr = sorted ? c->at<int32_t>(c->off_nbr) : nullptr;
+    if (sorted && c->D % 4 == 0 && c->D <= 256 && ((reinterpret_cast<uintptr_t>(c->points) & 15) == 0)) {
+        const int nv = (int)((c->D / 4 + 7) / 8);
+#define KMC_REFINE4(N)                                                                                          \
+    refine4_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, nbr, worklist, nw, \
+                                             labels)
+        if (nv <= 1) KMC_REFINE4(1);
+        else if (nv <= 2) KMC_REFINE4(2);
+        else if (nv <= 4) KMC_REFINE4(4);
+        else KMC_REFINE4(8);
+#undef KMC_REFINE4
+        KMC_CUDA(cudaGetLastError());
+        c->launches++;
+        return 0;
+    }
 #define KMC_REFINE(N)                                                                                       \
     do {                                                                                                    \
         if (sorted)                                                                                         \

@@ -122,6 +122,19 @@ def test_chunk_pipelined_accumulate(chunks, terms, pkg, cuda_device, monkeypatch
     assert stats["path"] == "tc"
 
 
+def test_tensor_fallback_on_poorly_separated_data(pkg, cuda_device):
+    """Points far from the origin with tiny spread: one fp16 MMA term cannot certify anything, so the
+    device-side gate must hand every chunk to the 3-term kernel (and the refine) -- same exact labels."""
+    # (one iteration per start: with coordinates near 1000 and a spread of 0.05 the fp32 rounding of the
+    # UPDATED centroids already moves distances by more than the 1e-5 near-tie window, so later iterations
+    # are not comparable with the float64 oracle on this data set)
+    for seed in (3, 4):
+        rng = np.random.default_rng(seed)
+        n, d, k = 20000, 64, 128
+        X = (1000.0 + rng.normal(0.0, 0.05, size=(n, d))).astype(np.float32)
+        _check_iterations(pkg, X, X[:k].copy(), 1, cuda_device, path="tc", form="diff")
+
+
 def test_unscaled_data_ranges_on_tensor_path(pkg, cuda_device):
     # tiny and huge magnitudes go through the power-of-two scaling of the fp16 planes
     for scale in (1e-6, 3e4):
