@@ -242,7 +242,7 @@ def main():
         X = pkg.datagen.image_torch(2160, 3840, SEED, dev)[r0:r1].contiguous()
         C0 = pkg.datagen.kmeanspp_init(X[:: max(1, n_local // 65536)].cpu().numpy(), K, SEED) if rank == 0 else None
     else:
-        X, _ = pkg.datagen.blobs_torch(n_local, D, K, SEED + rank, dev)
+        X, _ = pkg.datagen.blobs_torch(n_local, D, K, SEED, dev, stream=rank)   # same blobs on every rank
         C0 = X[:K].cpu().numpy() if rank == 0 else None
     c0_t = torch.from_numpy(C0).to(dev) if rank == 0 else torch.empty((K, D), dtype=torch.float32, device=dev)
     if world > 1:

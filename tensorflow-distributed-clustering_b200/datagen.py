@@ -30,8 +30,11 @@ def blobs_numpy(n: int, d: int, k: int, seed: int, sigma: float = 1.0, spread: f
 
 
 def blobs_torch(n: int, d: int, k: int, seed: int, device, sigma: float = 1.0, spread: float = 10.0,
-                block_rows: int = 1 << 22, out=None):
-    """Device blobs, generated block by block straight into HBM (no host copy of the data)."""
+                block_rows: int = 1 << 22, out=None, stream: int = 0):
+    """Device blobs, generated block by block straight into HBM (no host copy of the data).
+
+    `seed` fixes the blob centres; `stream` selects an independent stream of points around those same
+    centres (one per rank when a data set is generated shard by shard)."""
     import torch
 
     centers = torch.from_numpy(blob_centers(k, d, seed, spread)).to(device)
@@ -39,7 +42,7 @@ def blobs_torch(n: int, d: int, k: int, seed: int, device, sigma: float = 1.0, s
     gen = torch.Generator(device=device)
     for b, r0 in enumerate(range(0, n, block_rows)):
         r1 = min(n, r0 + block_rows)
-        gen.manual_seed(int(seed) * 1000003 + b)
+        gen.manual_seed((int(seed) * 1000003 + int(stream)) * 1009 + b)
         which = torch.randint(0, k, (r1 - r0,), generator=gen, device=device)
         blk = X[r0:r1]
         blk.normal_(0.0, sigma, generator=gen)
