@@ -1,78 +1,137 @@
 // Small-D path (HBM-bound configs, e.g. D=2/K=8 and D=3/K=16): ONE pass over the points does
 // distance, argmin and accumulation.  Centroids live in shared memory; each thread owns four
-// consecutive rows (4*D floats = D aligned float4 loads) and a private column of shared-memory
-// accumulators (conflict-free: bank = thread id), folded once per CTA into fp64 global partials.
+// consecutive rows (4*D floats = D aligned float4 loads, the next group prefetched while the current one
+// is processed) and a private column of shared-memory accumulators (conflict-free: bank = thread id),
+// folded once per CTA into fp64 global partials.  The grid is persistent (two CTAs per SM), so the
+// number of fp64 atomics per partial is a few hundred, not one per tile of rows.
+//
+// Arithmetic: the reference's exact difference form sum_j (x_j - c_j)^2, evaluated two rows at a time
+// with the packed fp32 pipe (add.f32x2 / fma.f32x2).  For K <= 64 the argmin runs on values that carry
+// the centroid index in their lowest mantissa bits (one LOP3 + half a 3-input FMNMX per candidate
+// instead of compare + two selects); the truncation is < 2^-17 relative, below the 1e-5 near-tie window,
+// and equal truncated values resolve to the lowest index.  NaN centroids never win.
 //
 // Replaces reference scripts/distribuitedClustering.py:221-234 (tile/sub/square/sum/argmin on
 // materialised [N,K,M] tensors), :237-242 (K x gather+mean) and :244-248 (CPU bincount, mean*count).
-// Distances use the reference's exact difference form sum_j (x_j - c_j)^2 (no cancellation);
-// ties go to the lowest centroid index (strict '<', ascending k), NaN centroids never win.
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
+#include <cstdlib>
 
 namespace kmc {
 
-constexpr int kSmallThreads = 128;
-constexpr int kSmallMaxSlots = 384;   // K*(D+1) accumulator slots per thread column
+constexpr int kSmallThreads = 256;
+constexpr int kSmallMaxSlots = 384;   // K*(D+1) accumulator slots per thread column (at 128 threads)
 
 bool small_path_supported(int64_t K, int64_t D) {
     return D >= 1 && D <= 8 && K >= 1 && K * (D + 1) <= kSmallMaxSlots;
 }
 
-template <int D, bool ACCUM, bool LABELS>
-__global__ void __launch_bounds__(kSmallThreads)
+template <int D>
+__device__ __forceinline__ void load_group(const float* __restrict__ x, int64_t n, int64_t g, int vec_ok,
+                                           float (&f)[4 * D]) {
+    const int64_t row0 = g << 2;
+    if (n - row0 >= 4 && vec_ok) {
+        const float4* p = reinterpret_cast<const float4*>(x + row0 * D);
+#pragma unroll
+        for (int q = 0; q < D; ++q) {
+            const float4 v = ld_stream_f4(p + q);
+            f[4 * q + 0] = v.x; f[4 * q + 1] = v.y; f[4 * q + 2] = v.z; f[4 * q + 3] = v.w;
+        }
+    } else {
+        const int valid = (n - row0 >= 4) ? 4 : (int)(n - row0);
+#pragma unroll
+        for (int e = 0; e < 4 * D; ++e) f[e] = (e < valid * D) ? x[row0 * D + e] : 0.f;
+    }
+}
+
+template <int D, int THREADS, bool ACCUM, bool LABELS, bool PACK>
+__global__ void __launch_bounds__(THREADS)
 small_kernel(const float* __restrict__ x, int64_t n, const float* __restrict__ cent, int K,
-             double* __restrict__ partials, int32_t* __restrict__ labels, int vec_ok) {
+             double* __restrict__ partials, int32_t* __restrict__ labels, int vec_ok, uint32_t idx_mask) {
     extern __shared__ __align__(16) float smem_f[];
-    float* cs = smem_f;                                   // [K*D] centroids
-    float* acc = smem_f + ((K * D + 3) & ~3);             // [K*(D+1)][kSmallThreads]
+    float* ncs = smem_f;                                  // [K*D] NEGATED centroids
+    float* acc = smem_f + ((K * D + 3) & ~3);             // [K*(D+1)][THREADS]
     const int tid = threadIdx.x;
     const int S = K * (D + 1);
 
-    for (int i = tid; i < K * D; i += kSmallThreads) cs[i] = cent[i];
+    for (int i = tid; i < K * D; i += THREADS) ncs[i] = -cent[i];
     if (ACCUM) {
-        for (int s = 0; s < S; ++s) acc[s * kSmallThreads + tid] = 0.f;
+        for (int s = 0; s < S; ++s) acc[s * THREADS + tid] = 0.f;
     }
     __syncthreads();
 
     float inertia = 0.f;
     const int64_t n_groups = (n + 3) >> 2;
-    for (int64_t g = (int64_t)blockIdx.x * kSmallThreads + tid; g < n_groups;
-         g += (int64_t)gridDim.x * kSmallThreads) {
+    const int64_t stride = (int64_t)gridDim.x * THREADS;
+    int64_t g = (int64_t)blockIdx.x * THREADS + tid;
+    float nxt[4 * D];
+    if (g < n_groups) load_group<D>(x, n, g, vec_ok, nxt);
+    for (; g < n_groups; g += stride) {
+        float f[4 * D];
+#pragma unroll
+        for (int e = 0; e < 4 * D; ++e) f[e] = nxt[e];
+        if (g + stride < n_groups) load_group<D>(x, n, g + stride, vec_ok, nxt);   // in flight during the math
         const int64_t row0 = g << 2;
         const int valid = (n - row0 >= 4) ? 4 : (int)(n - row0);
-        float xs[4 * D];
-        if (valid == 4 && vec_ok) {
-            const float4* p = reinterpret_cast<const float4*>(x + row0 * D);
+        // rows (0,1) and (2,3) as packed pairs per dimension
+        float2 xp[2][D];
 #pragma unroll
-            for (int q = 0; q < D; ++q) {
-                float4 v = ld_stream_f4(p + q);
-                xs[4 * q + 0] = v.x; xs[4 * q + 1] = v.y; xs[4 * q + 2] = v.z; xs[4 * q + 3] = v.w;
-            }
-        } else {
-#pragma unroll
-            for (int e = 0; e < 4 * D; ++e)
-                xs[e] = (e < valid * D) ? x[row0 * D + e] : 0.f;
+        for (int j = 0; j < D; ++j) {
+            xp[0][j] = make_float2(f[j], f[D + j]);
+            xp[1][j] = make_float2(f[2 * D + j], f[3 * D + j]);
         }
         float best[4];
         int bk[4];
 #pragma unroll
         for (int r = 0; r < 4; ++r) { best[r] = INFINITY; bk[r] = 0; }
-#pragma unroll 4
-        for (int k = 0; k < K; ++k) {
-            float c[D];
+
+        auto dist4 = [&](int k, float (&d)[4]) {
+            float2 d0, d1;
 #pragma unroll
-            for (int j = 0; j < D; ++j) c[j] = cs[k * D + j];
+            for (int j = 0; j < D; ++j) {
+                const float nc = ncs[k * D + j];
+                const float2 nc2 = make_float2(nc, nc);
+                const float2 t0 = __fadd2_rn(xp[0][j], nc2), t1 = __fadd2_rn(xp[1][j], nc2);
+                if (j == 0) { d0 = __fmul2_rn(t0, t0); d1 = __fmul2_rn(t1, t1); }
+                else { d0 = __ffma2_rn(t0, t0, d0); d1 = __ffma2_rn(t1, t1, d1); }
+            }
+            d[0] = d0.x; d[1] = d0.y; d[2] = d1.x; d[3] = d1.y;
+        };
+
+        if (PACK) {
+            int k = 0;
+            for (; k + 1 < K; k += 2) {
+                float da[4], db[4];
+                dist4(k, da);
+                dist4(k + 1, db);
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const float pa = __uint_as_float((__float_as_uint(da[r]) & idx_mask) | (uint32_t)k);
+                    const float pb = __uint_as_float((__float_as_uint(db[r]) & idx_mask) | (uint32_t)(k + 1));
+                    best[r] = fminf(fminf(best[r], pa), pb);
+                }
+            }
+            if (k < K) {
+                float da[4];
+                dist4(k, da);
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    best[r] = fminf(best[r], __uint_as_float((__float_as_uint(da[r]) & idx_mask) | (uint32_t)k));
+            }
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-                float t = xs[r * D] - c[0];
-                float d = t * t;
+                const uint32_t b = __float_as_uint(best[r]);
+                bk[r] = (best[r] < INFINITY) ? (int)(b & ~idx_mask) : 0;
+                best[r] = __uint_as_float(b & idx_mask);
+            }
+        } else {
+#pragma unroll 2
+            for (int k = 0; k < K; ++k) {
+                float d[4];
+                dist4(k, d);
 #pragma unroll
-                for (int j = 1; j < D; ++j) {
-                    t = xs[r * D + j] - c[j];
-                    d = fmaf(t, t, d);
-                }
-                if (d < best[r]) { best[r] = d; bk[r] = k; }
+                for (int r = 0; r < 4; ++r)
+                    if (d[r] < best[r]) { best[r] = d[r]; bk[r] = k; }
             }
         }
         if (LABELS) {
@@ -88,11 +147,11 @@ small_kernel(const float* __restrict__ x, int64_t n, const float* __restrict__ c
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
                 if (r < valid) {
-                    float* a = acc + (bk[r] * (D + 1)) * kSmallThreads + tid;
+                    float* a = acc + (bk[r] * (D + 1)) * THREADS + tid;
 #pragma unroll
-                    for (int j = 0; j < D; ++j) a[j * kSmallThreads] += xs[r * D + j];
-                    a[D * kSmallThreads] += 1.f;
-                    inertia += best[r];
+                    for (int j = 0; j < D; ++j) a[j * THREADS] += f[r * D + j];
+                    a[D * THREADS] += 1.f;
+                    if (best[r] < INFINITY) inertia += best[r];
                 }
             }
         }
@@ -101,10 +160,10 @@ small_kernel(const float* __restrict__ x, int64_t n, const float* __restrict__ c
     if (ACCUM) {
         __syncthreads();
         const int lane = tid & 31, warp = tid >> 5;
-        for (int s = warp; s < S; s += kSmallThreads / 32) {
+        for (int s = warp; s < S; s += THREADS / 32) {
             double v = 0.0;
 #pragma unroll
-            for (int q = 0; q < kSmallThreads / 32; ++q) v += (double)acc[s * kSmallThreads + q * 32 + lane];
+            for (int q = 0; q < THREADS / 32; ++q) v += (double)acc[s * THREADS + q * 32 + lane];
             v = warp_sum(v);
             if (lane == 0 && v != 0.0) {
                 const int k = s / (D + 1), j = s - k * (D + 1);
@@ -117,32 +176,53 @@ small_kernel(const float* __restrict__ x, int64_t n, const float* __restrict__ c
     }
 }
 
-template <int D>
-static int launch_small_d(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s) {
+template <int D, int THREADS>
+static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s) {
     const int K = (int)c->K;
     const size_t smem_c = (size_t)((K * D + 3) & ~3) * sizeof(float);
-    const size_t smem_acc = (size_t)K * (D + 1) * kSmallThreads * sizeof(float);
+    const size_t smem_acc = (size_t)K * (D + 1) * THREADS * sizeof(float);
     const size_t smem = smem_c + (accumulate ? smem_acc : 0);
     const int64_t n_groups = (c->n + 3) / 4;
-    int64_t blocks = (n_groups + kSmallThreads - 1) / kSmallThreads;
+    int64_t blocks = (n_groups + THREADS - 1) / THREADS;
+    // persistent grid: as many CTAs as stay resident, up to 1024 threads per SM (the loads in flight per SM,
+    // one 16*D-byte group per thread, are what reaches HBM bandwidth)
     int per_sm = (int)((200 * 1024) / (smem + 1024));
-    per_sm = per_sm < 1 ? 1 : (per_sm > 12 ? 12 : per_sm);
+    const int want = 1024 / THREADS;
+    per_sm = per_sm < 1 ? 1 : (per_sm > want ? want : per_sm);
+    if (const char* e = getenv("KMC_SMALL_CTAS")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;   // experiment knob
     const int64_t cap = (int64_t)c->sm_count * per_sm;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     const int vec_ok = ((reinterpret_cast<uintptr_t>(c->points) & 15) == 0) &&
                        (labels_out == nullptr || (reinterpret_cast<uintptr_t>(labels_out) & 15) == 0);
+    int bits = 1;
+    while ((1 << bits) < K) ++bits;
+    const bool pack = K <= 64;
+    const uint32_t idx_mask = ~((1u << bits) - 1u);
     auto launch = [&](auto kern) -> int {
         KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<(unsigned)blocks, kSmallThreads, smem, s>>>(c->points, c->n, c->centroids(), K, c->partials(),
-                                                           labels_out, vec_ok);
+        kern<<<(unsigned)blocks, THREADS, smem, s>>>(c->points, c->n, c->centroids(), K, c->partials(), labels_out,
+                                                     vec_ok, idx_mask);
         KMC_CUDA(cudaGetLastError());
         c->launches++;
         return 0;
     };
-    if (accumulate && labels_out) return launch(small_kernel<D, true, true>);
-    if (accumulate) return launch(small_kernel<D, true, false>);
-    return launch(small_kernel<D, false, true>);
+    if (pack) {
+        if (accumulate && labels_out) return launch(small_kernel<D, THREADS, true, true, true>);
+        if (accumulate) return launch(small_kernel<D, THREADS, true, false, true>);
+        return launch(small_kernel<D, THREADS, false, true, true>);
+    }
+    if (accumulate && labels_out) return launch(small_kernel<D, THREADS, true, true, false>);
+    if (accumulate) return launch(small_kernel<D, THREADS, true, false, false>);
+    return launch(small_kernel<D, THREADS, false, true, false>);
+}
+
+template <int D>
+static int launch_small_d(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s) {
+    // 256 threads per CTA when the private accumulator columns fit twice per SM, else 128
+    const size_t acc256 = (size_t)c->K * (D + 1) * 256 * sizeof(float);
+    if (!accumulate || acc256 <= 96 * 1024) return launch_small_dt<D, kSmallThreads>(c, accumulate, labels_out, s);
+    return launch_small_dt<D, 128>(c, accumulate, labels_out, s);
 }
 
 int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s) {

@@ -90,6 +90,7 @@ def test_golden_case_per_iteration(name, pkg, golden_index, cuda_device):
 
 @pytest.mark.parametrize("n,d,k,path", [
     (5000, 2, 8, "small"), (4097, 3, 16, "small"), (3001, 8, 40, "small"), (1, 2, 1, "small"),
+    (2003, 2, 100, "small"), (1501, 1, 150, "small"), (2500, 5, 64, "small"), (70001, 3, 16, "small"),
     (3000, 5, 7, "simt"), (2500, 20, 100, "simt"), (2049, 33, 65, "simt"), (4096, 32, 256, "simt"),
     (4000, 16, 32, "tc"), (3000, 32, 256, "tc"), (2500, 64, 300, "tc"), (2000, 128, 1024, "tc"),
     (1500, 100, 257, "tc"), (1200, 160, 96, "tc"), (1000, 256, 512, "tc"), (129, 64, 64, "tc"),
