@@ -126,6 +126,17 @@ double* kmc_partials_ptr(kmc_ctx* ctx);
 int64_t kmc_partials_len(const kmc_ctx* ctx);   /* = K*D + K + 2 */
 
 /*
+ * Out-of-core batches (points that do not fit in HBM at once): kmc_resize changes the number of rows
+ * of the NEXT batch (at most the n_rows of kmc_create; bind its points afterwards), and
+ * kmc_accumulate_add works like kmc_accumulate but ADDS the batch to the partial buffer instead of
+ * overwriting it, so several batches add up to one exact Lloyd iteration before kmc_update.
+ * Replaces the reference's batch loop (main :328-360, run_experiments :296-318), which instead runs
+ * an independent K-Means per batch and averages the end centres (:310).
+ */
+int kmc_resize(kmc_ctx* ctx, int64_t n_rows);
+int kmc_accumulate_add(kmc_ctx* ctx, void* stream);
+
+/*
  * Centroid update from the (all-reduced) partial buffer: c[k] = sums[k] / counts[k], the squared
  * centre shift, and on the tensor path the next iteration's split centroid planes and norms.
  * Replaces add_n / tile / div / transpose / assign on /cpu:0 (:257-263).

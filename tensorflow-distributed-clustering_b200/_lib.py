@@ -41,6 +41,8 @@ SIGNATURES = {
     "kmc_accumulate": (c_int, [c_void_p, c_void_p]),
     "kmc_partials_ptr": (c_void_p, [c_void_p]),
     "kmc_partials_len": (c_int64, [c_void_p]),
+    "kmc_resize": (c_int, [c_void_p, c_int64]),
+    "kmc_accumulate_add": (c_int, [c_void_p, c_void_p]),
     "kmc_update": (c_int, [c_void_p, c_void_p]),
     "kmc_iterate": (c_int, [c_void_p, c_int, c_double, POINTER(c_int), POINTER(c_double), POINTER(c_double), c_void_p]),
     "kmc_assign": (c_int, [c_void_p, c_void_p, c_void_p]),

@@ -83,7 +83,7 @@ class LloydShard:
         with torch.cuda.device(self.device):
             L.check(self.lib.kmc_bind_points(self._ctx, c_void_p(points.data_ptr()), self._stream()))
 
-    def stage_from_host(self, host, row0: int, batch_size=None):
+    def stage_from_host(self, host, row0: int, batch_size=None, out=None):
         """Pinned, chunked H2D of rows [row0, row0 + n_rows) of a host array, then bind them.
 
         Replaces feeding ``all_data`` and the per-GPU variable initialisation (:196-197, :217, :273).
@@ -100,7 +100,10 @@ class LloydShard:
                 raise ValueError("host array must be C-contiguous float32/float64")
             arr_ptr, is64 = host.ctypes.data, host.dtype == np.float64
         with torch.cuda.device(self.device):
-            pts = torch.empty((self.n, self.D), dtype=torch.float32, device=self.device)
+            if out is not None:
+                pts = out[:self.n]
+            else:
+                pts = torch.empty((self.n, self.D), dtype=torch.float32, device=self.device)
             step = self.n if not batch_size else max(1, int(batch_size))
             for r in range(0, self.n, max(step, 1)):
                 nr = min(step, self.n - r)
@@ -127,6 +130,17 @@ class LloydShard:
     def accumulate(self):
         with _torch().cuda.device(self.device):
             L.check(self.lib.kmc_accumulate(self._ctx, self._stream()))
+
+    def accumulate_add(self):
+        """Like accumulate(), but adds this batch to the partial buffer (out-of-core batches)."""
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_accumulate_add(self._ctx, self._stream()))
+
+    def resize(self, n_rows: int):
+        """Rows of the next batch (<= the size the shard was created for); bind its points afterwards."""
+        L.check(self.lib.kmc_resize(self._ctx, int(n_rows)))
+        self.n = int(n_rows)
+        self.points = None
 
     def update(self):
         with _torch().cuda.device(self.device):
@@ -242,13 +256,15 @@ def _as_host_matrix(data_batch):
 
 def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_iters=20, *,
                          seed=None, batch_size=None, tol=0.0, empty="keep", path="auto",
-                         return_labels=True):
+                         return_labels=True, out_of_core=None):
     """Data-parallel K-Means (Lloyd) on one or more B200s -- drop-in for the reference function.
 
     Accepts both reference call shapes: ``(data_batch, K, GPU_names, initial_centers,
     n_max_iters)`` (how ``run_experiments`` calls it, :303) and HEAD's ``(data_batch, K,
     GPU_names, n_max_iters)`` (:180), where the centres come from k-means++ (:191; seeded here by
-    ``seed``).  ``GPU_names`` is a list of device names as returned by the reference's
+    ``seed``).  ``out_of_core``: keep the rows in host memory and stream them through the GPUs in
+    batches of ``batch_size`` rows every iteration (exact Lloyd across batches); None = only when a
+    shard does not fit in HBM.  ``GPU_names`` is a list of device names as returned by the reference's
     ``get_available_gpus()`` (or an int = number of GPUs).  ``batch_size`` = rows per pinned H2D
     staging chunk; ``tol`` = optional early stop on the squared centre shift (0 = run all
     ``n_max_iters`` like the reference).
@@ -285,6 +301,14 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     if init_center.shape != (K, D):
         raise ValueError(f"initial_centers shape {init_center.shape} != {(K, D)}")
 
+    if out_of_core is None:
+        out_of_core = (not on_device) and not all(
+            _fits_in_hbm(r1 - r0, D, K, torch.device("cuda", dev), empty, path) for dev, (r0, r1) in zip(dev_ids, ranges))
+    if out_of_core:
+        if on_device:
+            raise ValueError("out_of_core needs the rows in host memory")
+        return _k_means_out_of_core(data, K, dev_ids, ranges, init_center, n_max_iters, batch_size, tol, empty, path,
+                                    return_labels, setup_ts)
     shards = [LloydShard(r1 - r0, D, K, torch.device("cuda", dev), empty=empty, path=path)
               for dev, (r0, r1) in zip(dev_ids, ranges)]
     setup_time = float(time.time() - setup_ts)
@@ -346,6 +370,78 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     }
 
 
+class _OutOfCoreShard:
+    """One GPU's share of the rows when they do not fit in HBM together: the rows stay in host memory
+    and are streamed through one device buffer of `batch_rows` rows.  Presents the interface
+    lloyd_loop needs; accumulate() = stage + bind + kmc_accumulate_add for every batch, so several
+    batches add up to ONE exact Lloyd iteration (the reference instead clusters every batch on its own
+    and averages the end centres, :296-318)."""
+
+    def __init__(self, host, r0, r1, K, device, batch_rows, empty, path):
+        torch = _torch()
+        self.host, self.r0, self.r1 = host, int(r0), int(r1)
+        self.batch_rows = int(min(batch_rows, max(1, r1 - r0)))
+        D = int(host.shape[1])
+        self.inner = LloydShard(self.batch_rows, D, K, device, empty=empty, path=path)
+        with torch.cuda.device(self.inner.device):
+            self.buf = torch.empty((self.batch_rows, D), dtype=torch.float32, device=self.inner.device)
+        self.device = self.inner.device
+
+    @property
+    def partials(self):
+        return self.inner.partials
+
+    def _batches(self):
+        for b0 in range(self.r0, self.r1, self.batch_rows):
+            yield b0, min(self.r1, b0 + self.batch_rows)
+
+    def _load(self, b0, b1):
+        self.inner.resize(b1 - b0)
+        self.inner.stage_from_host(self.host, b0, None, out=self.buf)
+
+    def set_centroids(self, C):
+        self.inner.set_centroids(C)
+
+    def get_centroids(self):
+        return self.inner.get_centroids()
+
+    def accumulate(self):
+        self.inner.partials.zero_()
+        for b0, b1 in self._batches():
+            self._load(b0, b1)
+            self.inner.accumulate_add()
+
+    def update(self):
+        self.inner.update()
+
+    def stats(self):
+        return self.inner.stats()
+
+    def assign_to_host(self, out):
+        """Labels of rows [r0, r1) into the pinned int64 tensor `out` (indexed by global row)."""
+        torch = _torch()
+        for b0, b1 in self._batches():
+            self._load(b0, b1)
+            out[b0:b1].copy_(self.inner.assign().to(torch.int64), non_blocking=True)
+        torch.cuda.synchronize(self.device)
+
+    def close(self):
+        self.inner.close()
+
+
+def _fits_in_hbm(n_rows, D, K, device, empty, path) -> bool:
+    """Would a resident shard of n_rows (points + workspace) fit in the free memory of `device`?"""
+    torch = _torch()
+    lib = L.load()
+    ctx = c_void_p()
+    flags = L.PATH_FLAGS[path]
+    L.check(lib.kmc_create(byref(ctx), torch.device(device).index or 0, int(n_rows), int(D), int(K), flags))
+    need = int(lib.kmc_workspace_bytes(ctx)) + int(n_rows) * int(D) * 4
+    lib.kmc_destroy(ctx)
+    free, _total = torch.cuda.mem_get_info(torch.device(device))
+    return need <= 0.92 * free
+
+
 def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *, device=None, batch_size=None,
                               tol=0.0, empty="keep", path="auto", return_labels=True, group=None):
     """The same Lloyd loop with ONE PROCESS PER GPU (torchrun): every rank passes the rows the
@@ -396,6 +492,47 @@ def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *,
         "computation_time": computation_time, "n_iter": n_iter, "inertia": inertia,
         "center_shift": float(np.sqrt(shift2)) if shift2 == shift2 else float("nan"),
         "converged": bool(tol > 0.0 and shift2 <= tol),
+    }
+
+
+def _k_means_out_of_core(data, K, dev_ids, ranges, init_center, n_max_iters, batch_size, tol, empty, path,
+                         return_labels, setup_ts):
+    torch = _torch()
+    N, D = int(data.shape[0]), int(data.shape[1])
+    shards = []
+    for dev, (r0, r1) in zip(dev_ids, ranges):
+        device = torch.device("cuda", dev)
+        rows = int(batch_size) if batch_size else (r1 - r0)
+        while rows > 1024 and not _fits_in_hbm(rows, D, K, device, empty, path):
+            rows = (rows + 1) // 2                      # largest power-of-two fraction of the shard that fits
+        shards.append(_OutOfCoreShard(data, r0, r1, K, device, rows, empty, path))
+    setup_time = float(time.time() - setup_ts)
+    initialization_ts = time.time()
+    for s in shards:
+        s.set_centroids(init_center)
+    initialization_time = float(time.time() - initialization_ts)   # the rows are re-staged every iteration
+    aux_ts = time.time()
+    n_iter, inertia, shift2 = lloyd_loop(shards, n_max_iters, tol)
+    for s in shards:
+        torch.cuda.synchronize(s.device)
+    computation_time = float(time.time() - aux_ts)
+    end_center = shards[0].get_centroids()
+    cluster_idx = last_labels = None
+    if return_labels:
+        out = torch.empty(N, dtype=torch.int64, pin_memory=True)
+        for s in shards:
+            s.assign_to_host(out)
+        cluster_idx = out.numpy()
+        last_labels = cluster_idx[ranges[-1][0]:ranges[-1][1]]
+    for s in shards:
+        s.close()
+    return {
+        "end_center": end_center, "cluster_idx": cluster_idx, "centroids": last_labels, "init_center": init_center,
+        "setup_time": setup_time, "initialization_time": initialization_time, "computation_time": computation_time,
+        "n_iter": n_iter, "inertia": inertia,
+        "center_shift": float(np.sqrt(shift2)) if shift2 == shift2 else float("nan"),
+        "converged": bool(tol > 0.0 and shift2 <= tol), "out_of_core": True,
+        "batch_rows": [s.batch_rows for s in shards],
     }
 
 

@@ -188,7 +188,7 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
     if (!c) KMC_FAIL(KMC_E_NOMEM, "host allocation failed");
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
-    c->n = n_rows; c->D = D; c->K = K; c->flags = flags;
+    c->n = n_rows; c->n_cap = n_rows; c->D = D; c->K = K; c->flags = flags;
     int path = (int)(flags & KMC_PATH_MASK);
     if (path == KMC_PATH_AUTO) {
         if (small_path_supported(K, D)) path = KMC_PATH_SMALL;
@@ -378,11 +378,28 @@ float* kmc_centroids_ptr(kmc_ctx* c) { return (c && c->ws) ? c->centroids() : nu
 double* kmc_partials_ptr(kmc_ctx* c) { return (c && c->ws) ? c->partials() : nullptr; }
 int64_t kmc_partials_len(const kmc_ctx* c) { return c ? c->K * c->D + c->K + 2 : 0; }
 
-int kmc_accumulate(kmc_ctx* c, void* stream) {
+int kmc_resize(kmc_ctx* c, int64_t n_rows) {
+    if (!c) KMC_FAIL(KMC_E_INVALID, "null context");
+    if (n_rows < 0 || n_rows > c->n_cap)
+        KMC_FAIL(KMC_E_INVALID, "kmc_resize: %lld rows outside [0, %lld], the size the context was created for",
+                 (long long)n_rows, (long long)c->n_cap);
+    c->n = n_rows;
+    c->points = nullptr;          // the next batch must be bound before use
+    c->tmaps_ready = false;
+    return 0;
+}
+
+static int accumulate_impl(kmc_ctx* c, void* stream, bool zero);
+
+int kmc_accumulate(kmc_ctx* c, void* stream) { return accumulate_impl(c, stream, true); }
+
+int kmc_accumulate_add(kmc_ctx* c, void* stream) { return accumulate_impl(c, stream, false); }
+
+static int accumulate_impl(kmc_ctx* c, void* stream, bool zero) {
     KMC_TRY(check_ready(c, true));
     KMC_CUDA(cudaSetDevice(c->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    KMC_CUDA(cudaMemsetAsync(c->partials(), 0, (size_t)kmc_partials_len(c) * 8, s));
+    if (zero) KMC_CUDA(cudaMemsetAsync(c->partials(), 0, (size_t)kmc_partials_len(c) * 8, s));
     if (c->n == 0) return 0;
     const int slot = c->prof_acc_n;
     KMC_TRY(prof_mark(c, slot, 0, s));
@@ -390,7 +407,7 @@ int kmc_accumulate(kmc_ctx* c, void* stream) {
         KMC_TRY(launch_small(c, true, nullptr, s));
         KMC_TRY(prof_mark(c, slot, 1, s));
         KMC_TRY(prof_mark(c, slot, 2, s));
-    } else if (c->path == KMC_PATH_TC && c->n_chunks > 1) {
+    } else if (c->path == KMC_PATH_TC && c->n_chunks > 1 && c->n >= 4 * kTcBlockM) {
         // chunk-pipelined tensor path: the caller's stream runs the tensor kernel over one row chunk after
         // the other; the side stream follows one chunk behind with the exact refine, the counting sort and
         // the segmented sums of the finished chunk (its CTAs share the SMs with the persistent tensor CTAs)

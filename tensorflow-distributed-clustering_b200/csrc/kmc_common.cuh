@@ -62,6 +62,7 @@ struct kmc_ctx {
     int device = 0;
     int sm_count = 0;
     int64_t n = 0, D = 0, K = 0;
+    int64_t n_cap = 0;                  // rows the workspace was laid out for (kmc_resize keeps n <= n_cap)
     uint32_t flags = 0;
     int path = 0;                       // KMC_PATH_*
     // tensor-path geometry

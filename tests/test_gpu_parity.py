@@ -269,3 +269,19 @@ def test_size_independent_properties_large(pkg, cuda_device):
     assert len(oracle.label_mismatches(lab1.cpu().numpy()[idx], ref, d1, d2, TIE_RTOL)) == 0
     assert abs(part[k * d + k] - d1.sum() * (n / 4096)) < 0.05 * part[k * d + k]
     s.close()
+
+
+@pytest.mark.parametrize("n,d,k,batch", [(10007, 2, 8, 3000), (9001, 64, 128, 4096)])
+def test_out_of_core_batches_are_one_exact_lloyd_run(n, d, k, batch, pkg, cuda_device):
+    """Rows kept in host memory and streamed in batches every iteration (kmc_resize /
+    kmc_accumulate_add) must give the same run as resident rows: batches add up to ONE Lloyd iteration."""
+    X, _ = pkg.datagen.blobs_numpy(n, d, k, seed=77)
+    C0 = X[:k].copy()
+    res = pkg.distribuited_k_means(X, k, 1, C0, 5, batch_size=batch, out_of_core=True)
+    assert res["out_of_core"] and res["batch_rows"] == [batch]
+    ref = oracle.run_lloyd(X, C0, 5, form="gemm" if d * k > 4096 else "diff")
+    assert oracle.rel_err(res["end_center"], ref["end_center"]) <= RTOL
+    assert len(oracle.label_mismatches(res["cluster_idx"], ref["cluster_idx"], ref["final_d1"], ref["final_d2"])) == 0
+    assert abs(res["inertia"] - ref["history"][-1]["inertia"]) <= RTOL * ref["history"][-1]["inertia"]
+    resident = pkg.distribuited_k_means(X, k, 1, C0, 5)
+    assert oracle.rel_err(res["end_center"], resident["end_center"]) <= 1e-6
