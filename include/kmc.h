@@ -194,6 +194,19 @@ int kmc_get_phase_ms(kmc_ctx* ctx, float* out_ms, int n);
 int kmc_debug_tc_scores(kmc_ctx* ctx, float* dev_scores, void* stream);
 
 /*
+ * Seeded k-means++ (D^2 sampling) on the device: K rows of dev_points [n_rows, D] are drawn into
+ * dev_centroids [K, D]; the rows chosen are optionally returned in host_chosen_rows [K].  The same
+ * seed gives the same centres (the K uniform numbers are a splitmix64 stream of `seed`).
+ * dev_scratch needs kmc_kmeanspp_scratch_bytes(n_rows, K) bytes.  Needs no kmc_ctx.
+ * Replaces `k_means_._init_centroids(data_batch, K, init='k-means++')` (reference :191), which is
+ * host-side, private sklearn API and unseeded.
+ */
+int64_t kmc_kmeanspp_scratch_bytes(int64_t n_rows, int64_t K);
+int kmc_kmeanspp(int device, const float* dev_points, int64_t n_rows, int64_t D, int64_t K, uint64_t seed,
+                 float* dev_centroids, int64_t* host_chosen_rows, void* dev_scratch, int64_t scratch_bytes,
+                 void* stream);
+
+/*
  * Per-cluster sums, counts and inertia from labels the caller already has, WITHOUT any device
  * allocation and without a kmc_ctx or workspace.  No counterpart in the reference.
  *

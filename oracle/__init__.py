@@ -14,6 +14,7 @@ independent implementation of the same math, ``sklearn.cluster.KMeans(algorithm=
 (``tests/golden/make_golden.py``), but it could not be checked against outputs of the
 reference itself.
 """
+from . import kmeanspp_oracle  # noqa: F401  (restatement of the device k-means++, csrc/kmeanspp.cu)
 from .kmeans_oracle import (  # noqa: F401
     shard_sizes,
     dist2,

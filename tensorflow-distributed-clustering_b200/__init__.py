@@ -12,13 +12,14 @@ from .api import (  # noqa: F401
     allreduce_partials_single_process,
     distribuited_k_means,
     distribuited_k_means_spmd,
+    kmeanspp_device,
     lloyd_loop,
     run_experiments,
 )
 from .sharding import parse_gpu_names, shard_ranges, shard_sizes  # noqa: F401
 
 __all__ = [
-    "LloydShard", "distribuited_k_means", "distribuited_k_means_spmd", "run_experiments", "lloyd_loop",
+    "LloydShard", "distribuited_k_means", "distribuited_k_means_spmd", "kmeanspp_device", "run_experiments", "lloyd_loop",
     "allreduce_partials_single_process", "shard_sizes", "shard_ranges", "parse_gpu_names",
     "datagen", "sharding",
 ]

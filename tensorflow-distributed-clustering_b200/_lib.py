@@ -50,6 +50,9 @@ SIGNATURES = {
     "kmc_set_param": (c_int, [c_void_p, c_int, c_double]),
     "kmc_get_phase_ms": (c_int, [c_void_p, POINTER(c_float), c_int]),
     "kmc_debug_tc_scores": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "kmc_kmeanspp_scratch_bytes": (c_int64, [c_int64, c_int64]),
+    "kmc_kmeanspp": (c_int, [c_int, c_void_p, c_int64, c_int64, c_int64, ctypes.c_uint64, c_void_p, c_void_p, c_void_p,
+                             c_int64, c_void_p]),
     "kmc_cluster_sums_noalloc": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64,
                                          c_void_p, c_void_p]),
 }

@@ -193,6 +193,49 @@ class LloydShard:
         return out
 
 
+def kmeanspp_device(points, K: int, seed, max_rows: int = 1 << 20):
+    """Seeded k-means++ on the GPU (kmc_kmeanspp).  `points`: [N, D] float CUDA tensor, or a host array /
+    CPU tensor, in which case a seeded uniform subsample of at most `max_rows` rows is uploaded first.
+    Returns (centres float32 ndarray [K, D], chosen row indices into `points`).
+    Replaces the reference's host-side, unseeded `k_means_._init_centroids(..., init='k-means++')` (:191)."""
+    torch = _torch()
+    lib = L.load()
+    seed = 0 if seed is None else int(seed) & ((1 << 64) - 1)
+    N = int(points.shape[0])
+    rng = np.random.default_rng(seed)
+    sub_idx = None
+    if isinstance(points, torch.Tensor) and points.is_cuda:
+        device = points.device
+        if N > max_rows:
+            sub_idx = np.sort(rng.choice(N, max_rows, replace=False))
+            pts = points[torch.from_numpy(sub_idx).to(device)].to(torch.float32).contiguous()
+        else:
+            pts = points.to(torch.float32).contiguous()
+    else:
+        device = torch.device("cuda", torch.cuda.current_device())
+        host = points.numpy() if isinstance(points, torch.Tensor) else np.asarray(points)
+        if N > max_rows:
+            sub_idx = np.sort(rng.choice(N, max_rows, replace=False))
+            host = host[sub_idx]
+        pts = torch.from_numpy(np.ascontiguousarray(host, dtype=np.float32)).to(device)
+    n, D = int(pts.shape[0]), int(pts.shape[1])
+    if K > n:
+        raise ValueError(f"K={K} clusters but only {n} candidate rows")
+    with torch.cuda.device(device):
+        nbytes = int(lib.kmc_kmeanspp_scratch_bytes(n, int(K)))
+        scratch = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+        cent = torch.empty((int(K), D), dtype=torch.float32, device=device)
+        chosen = np.empty(int(K), dtype=np.int64)
+        stream = c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        L.check(lib.kmc_kmeanspp(device.index or 0, c_void_p(pts.data_ptr()), n, D, int(K), ctypes.c_uint64(seed),
+                                 c_void_p(cent.data_ptr()), c_void_p(chosen.ctypes.data), c_void_p(scratch.data_ptr()),
+                                 nbytes, stream))
+        centres = cent.cpu().numpy()
+    if sub_idx is not None:
+        chosen = sub_idx[chosen]
+    return centres, chosen
+
+
 # ---------------------------------------------------------------------------------------------
 # Cross-shard reduction (the reference's add_n on /cpu:0, :257-258)
 # ---------------------------------------------------------------------------------------------
@@ -295,8 +338,8 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     on_device = isinstance(data, torch.Tensor) and data.is_cuda
 
     if initial_centers is None:                                               # :191
-        host_view = data.detach().cpu().numpy() if isinstance(data, torch.Tensor) else data
-        initial_centers = kmeanspp_init(host_view, K, seed)
+        with torch.cuda.device(torch.device("cuda", dev_ids[0])):
+            initial_centers, _ = kmeanspp_device(data, K, seed)
     init_center = np.array(initial_centers, dtype=np.float32, copy=True)
     if init_center.shape != (K, D):
         raise ValueError(f"initial_centers shape {init_center.shape} != {(K, D)}")

@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(HERE, "libkmc_b200.so")
 
 SOURCES = [
     "kmc_api.cu", "stage.cu", "assign_small.cu", "assign_simt.cu", "assign_tc.cu",
-    "accumulate.cu", "update.cu", "refine.cu",
+    "accumulate.cu", "update.cu", "refine.cu", "kmeanspp.cu",
 ]
 HEADERS = ["kmc_common.cuh", "kmc_device.cuh", os.path.join("..", "..", "include", "kmc.h")]
 

@@ -285,3 +285,28 @@ def test_out_of_core_batches_are_one_exact_lloyd_run(n, d, k, batch, pkg, cuda_d
     assert abs(res["inertia"] - ref["history"][-1]["inertia"]) <= RTOL * ref["history"][-1]["inertia"]
     resident = pkg.distribuited_k_means(X, k, 1, C0, 5)
     assert oracle.rel_err(res["end_center"], resident["end_center"]) <= 1e-6
+
+
+def test_device_kmeanspp_matches_its_cpu_restatement(pkg, cuda_device):
+    """kmc_kmeanspp against oracle/kmeanspp_oracle.py on integer-valued data (every squared distance is
+    exact in float32, so the device must choose exactly the same rows), plus the seeded 4-positional
+    form of the entry point (reference :180, :191)."""
+    import torch
+    from oracle.kmeanspp_oracle import kmeanspp
+
+    rng = np.random.default_rng(5)
+    for n, d, k in [(5000, 3, 16), (2500, 17, 40), (1100, 2, 8)]:
+        X = rng.integers(-20, 21, size=(n, d)).astype(np.float32)
+        for seed in (1, 123128):
+            want_c, want_rows = kmeanspp(X, k, seed)
+            got_c, got_rows = pkg.kmeanspp_device(torch.from_numpy(X).to(cuda_device), k, seed)
+            assert np.array_equal(got_rows, want_rows), (n, d, k, seed)
+            assert np.array_equal(got_c, want_c)
+    # through the entry point: same seed -> same centres, centres are rows of the data
+    X, _ = pkg.datagen.blobs_numpy(20000, 2, 8, seed=2)
+    a = pkg.distribuited_k_means(X, 8, 1, 3, seed=7)
+    b = pkg.distribuited_k_means(X, 8, 1, 3, seed=7)
+    assert np.array_equal(a["init_center"], b["init_center"]) and np.array_equal(a["end_center"], b["end_center"])
+    assert all((X == c).all(1).any() for c in a["init_center"])
+    ref = oracle.run_lloyd(X, a["init_center"], 3)
+    assert oracle.rel_err(a["end_center"], ref["end_center"]) <= RTOL

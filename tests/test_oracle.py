@@ -104,3 +104,19 @@ def test_golden_fixtures_reproduce(pkg, golden_index):
             assert abs(h["inertia"] - z["inertia"][t]) <= 1e-10 * abs(z["inertia"][t]), (name, t)
             assert np.array_equal(h["labels"], z["labels"][t]), (name, t)
         assert np.array_equal(res["cluster_idx"], z["cluster_idx"]), name
+
+
+def test_kmeanspp_oracle_is_seeded_and_spreads_centres(pkg):
+    from oracle.kmeanspp_oracle import kmeanspp, splitmix64_uniforms
+
+    u = splitmix64_uniforms(123128, 5)
+    assert ((u >= 0) & (u < 1)).all() and len(set(u.tolist())) == 5
+    X, centres = pkg.datagen.blobs_numpy(3000, 2, 6, seed=4)
+    c1, rows1 = kmeanspp(X, 6, seed=9)
+    c2, rows2 = kmeanspp(X, 6, seed=9)
+    assert np.array_equal(rows1, rows2) and np.array_equal(c1, X[rows1])
+    assert len(set(rows1.tolist())) == 6
+    # D^2 sampling on well separated blobs picks (almost surely) one point of every blob
+    owner = np.argmin(((c1[:, None, :] - centres[None, :, :]) ** 2).sum(2), axis=1)
+    assert len(set(owner.tolist())) >= 5
+    assert not np.array_equal(kmeanspp(X, 6, seed=10)[1], rows1)
