@@ -395,15 +395,22 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     else { m2 = fminf(m2, o1); }
                 }
             }
-            if (half == 0) {
+            if (half == 0) {                                 // warp-uniform
+                bool amb = false;
                 if (row_ok) {
                     if (a1 >= p.K) a1 = 0;
                     p.labels[row] = a1;
                     const float pack_err = kPackRel * (fabsf(m1) + fabsf(m2));
-                    if (p.worklist && (m2 - m1) <= thr + pack_err) {
-                        const unsigned long long pos = atomicAdd(p.amb_counter, 1ull);
-                        p.worklist[pos] = (int32_t)row;
-                    }
+                    amb = p.worklist && (m2 - m1) <= thr + pack_err;
+                }
+                // one atomic per warp reserves the worklist slots of all its uncertified rows
+                const unsigned mask = __ballot_sync(0xffffffffu, amb);
+                if (mask) {
+                    const int leader = __ffs(mask) - 1;
+                    unsigned long long base = 0;
+                    if (lane == leader) base = atomicAdd(p.amb_counter, (unsigned long long)__popc(mask));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    if (amb) p.worklist[base + __popc(mask & ((1u << lane) - 1u))] = (int32_t)row;
                 }
             }
             if (!(NPASS == 1 && kGroups == 2)) asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");

@@ -251,7 +251,7 @@ void kmc_destroy(kmc_ctx* c) {
     }
     if (c->amb_host) cudaFreeHost(c->amb_host);
     if (c->amb_event) cudaEventDestroy(c->amb_event);
-    if (c->side_stream) cudaStreamDestroy(c->side_stream);
+    if (c->side_stream) { cudaStreamSynchronize(c->side_stream); cudaStreamDestroy(c->side_stream); }
     for (auto& e : c->chunk_done)
         if (e) cudaEventDestroy(e);
     if (c->side_done) cudaEventDestroy(c->side_done);
