@@ -28,6 +28,8 @@
 // distance computation a dense contraction.
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
+#include <cstdlib>
+#include <type_traits>
 
 namespace kmc {
 
@@ -55,6 +57,7 @@ struct TcParams {
     float* scores;       // debug: [n, K] or nullptr
     float gamma;         // accumulate + split error of the 3-term score, relative to |X'||C'|
     float gamma1;        // accumulate error of the 1-term score
+    int use_bias_mma;    // this launch is one of the AUG / plain pair: run only if AUG matches the device-side check
     uint32_t pack_mask;  // 0xFFFFFF80, see pack_idx
 };
 
@@ -64,11 +67,15 @@ template <int KC, int NPASS> struct TcCfg {
     static constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
     static constexpr int kStages = (KC == 1 && NPASS == 3) ? 4 : 3;
     static constexpr uint32_t kBBytes = kStages * kStageBytesB;
-    static constexpr uint32_t kOther = kBBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 256;
+    // 1 term: a constant 128 x 64 fp16 tile holding kBiasConst in its first columns; multiplied with a stage
+    // of the bias plane it makes the MMA add S*|c_k|^2 to the accumulator (no FADD per score in the epilogue)
+    static constexpr uint32_t kAExtBytes = (NPASS == 1) ? kTileBytesA : 0;
+    static constexpr uint32_t kOther = kBBytes + kAExtBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 256;
     // the points tile is double buffered whenever two copies fit next to the B ring (227 KB per CTA)
     static constexpr int kABufs = (2 * kPlanes * KC * kTileBytesA + kOther <= 232448u) ? 2 : 1;
     static constexpr uint32_t kABytes = kABufs * kPlanes * KC * kTileBytesA;
-    static constexpr uint32_t kCnOff = kABytes + kBBytes;
+    static constexpr uint32_t kAExtOff = kABytes + kBBytes;
+    static constexpr uint32_t kCnOff = kAExtOff + kAExtBytes;
     // 3 terms: 2 x 256 bias floats staged per tile by the whole epilogue; 1 term: 128 floats per epilogue warp.
     // Either region doubles as the buffer that merges the two column halves of a row (384 floats).
     // (with 1 term the merge has its own 1536 bytes behind the per-warp slices, so it needs no block barrier)
@@ -130,15 +137,18 @@ __device__ __forceinline__ void top2_pair(Top2& t, float p0, float p1) {
 }
 
 // 32 accumulator columns of one row (column j0 + 0..31 of the warp's half tile)
-template <bool SCORES, bool USE_OFF>
+template <bool SCORES, bool USE_OFF, bool USE_CN>
 __device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float* __restrict__ cn, float off, int j0,
                                           uint32_t mask, Top2& e, Top2& o, float* __restrict__ score_row, int kbase, int K,
                                           float inv_s) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-        const float4 c4 = *reinterpret_cast<const float4*>(cn + 4 * q);
-        float v0 = __uint_as_float(r[4 * q + 0]) + c4.x, v1 = __uint_as_float(r[4 * q + 1]) + c4.y;
-        float v2 = __uint_as_float(r[4 * q + 2]) + c4.z, v3 = __uint_as_float(r[4 * q + 3]) + c4.w;
+        float v0 = __uint_as_float(r[4 * q + 0]), v1 = __uint_as_float(r[4 * q + 1]);
+        float v2 = __uint_as_float(r[4 * q + 2]), v3 = __uint_as_float(r[4 * q + 3]);
+        if (USE_CN) {
+            const float4 c4 = *reinterpret_cast<const float4*>(cn + 4 * q);
+            v0 += c4.x; v1 += c4.y; v2 += c4.z; v3 += c4.w;
+        }
         if (USE_OFF) { v0 += off; v1 += off; v2 += off; v3 += off; }
         top2_pair(e, pack_idx(v0, j0 + 4 * q + 0, mask), pack_idx(v1, j0 + 4 * q + 1, mask));
         top2_pair(o, pack_idx(v2, j0 + 4 * q + 2, mask), pack_idx(v3, j0 + 4 * q + 3, mask));
@@ -151,12 +161,18 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float* 
     }
 }
 
-template <int KC, bool SCORES, int NPASS, int EW>   // EW = epilogue warps (8 or 16)
-__global__ void __launch_bounds__(128 + 32 * EW, 1)
+template <int KC, bool SCORES, int NPASS, int EW, bool AUG>   // EW = epilogue warps; AUG = bias through the MMA
+__global__ void __maxnreg__(128)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
-                 const __grid_constant__ CUtensorMap tm_c, const TcParams p) {
+                 const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_bias,
+                 const TcParams p) {
     using Cfg = TcCfg<KC, NPASS>;
     if (p.gate_flag && *p.gate_flag == 0u) return;     // uniform for the whole grid
+    // bias through the MMA (AUG): only with one term (shared memory for the extra tile) and while the fp16
+    // pieces of the bias plane can represent every S*|c_k|^2.  That is a device-side fact, so the host launches
+    // the AUG and the plain variant back to back and exactly one of them runs (uniform for the whole grid).
+    constexpr bool aug = AUG;
+    if (p.use_bias_mma && AUG != (__uint_as_float(p.stats->cn_max_bits) < kBiasMax)) return;
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t smem_base = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -186,6 +202,19 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         tmem_alloc(smem_u32(tmem_slot), kTmemCols);
         tmem_relinquish();
     }
+    if (AUG) {
+        // constant A tile of the bias step, in the 128-byte-swizzled K-major layout TMA would produce:
+        // row r, 16-byte chunk c lives at r*128 + ((c ^ (r & 7)) << 4); only chunk 0 is non-zero
+        uint4* ext = reinterpret_cast<uint4*>(smem + Cfg::kAExtOff);
+        for (int i = threadIdx.x; i < (int)(kTileBytesA / 16); i += blockDim.x) ext[i] = make_uint4(0u, 0u, 0u, 0u);
+        __syncthreads();
+        if (threadIdx.x < kTcBlockM) {
+            __half* row = reinterpret_cast<__half*>(smem + Cfg::kAExtOff + threadIdx.x * 128 + ((threadIdx.x & 7) << 4));
+#pragma unroll
+            for (int i = 0; i < kBiasPieces; ++i) row[i] = __float2half_rn(kBiasConst[i]);
+        }
+        fence_proxy_async();       // generic-proxy writes -> visible to the tensor core's async proxy
+    }
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -212,6 +241,14 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             load_a(0);
             for (int it = 0; it < n_my_tiles; ++it) {
                 for (int nt = 0; nt < p.n_ntiles; ++nt) {
+                    if (aug) {      // stage of the bias plane: 256 centroids x one 64-column chunk
+                        const int slot = sb % Cfg::kStages;
+                        mbar_wait<100>(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x280u + slot);
+                        mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
+                        tma_load_2d_hint(smem_base + Cfg::kABytes + slot * kStageBytesB, &tm_bias, 0, nt * kTcBlockN,
+                                         b_full(slot), kEvictLast);
+                        ++sb;
+                    }
                     for (int kc = 0; kc < KC; ++kc) {
 #pragma unroll
                         for (int pl = 0; pl < ((NPASS == 1) ? 1 : 2); ++pl) {
@@ -244,6 +281,16 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     tc_fence_after_sync();
                     const uint32_t d_tmem = tmem_base + buf * kTcBlockN;
                     uint32_t accum = 0;
+                    if (aug) {      // accumulator := S*|c_k|^2 (one k-step: constants x bias pieces)
+                        const int slot = sb % Cfg::kStages;
+                        mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x580u + slot);
+                        tc_fence_after_sync();
+                        umma_f16(d_tmem, umma_desc_sw128(smem_base + Cfg::kAExtOff),
+                                 umma_desc_sw128(smem_base + Cfg::kABytes + slot * kStageBytesB), kInstrDesc, 0);
+                        accum = 1;
+                        umma_commit(b_empty(slot));
+                        ++sb;
+                    }
                     for (int kc = 0; kc < KC; ++kc) {
                         // stage with the centroid hi plane: x_hi*c_hi, then x_lo*c_hi
                         int slot = sb % Cfg::kStages;
@@ -319,8 +366,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             int a_e = 0, a_o = 0;
             for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                 const uint32_t buf = ac & 1u;
-                const float* cn;
-                if (NPASS == 1) {
+                const float* cn = cn_s;
+                if (aug) {
+                    // the MMA already added the biases: nothing to stage
+                } else if (NPASS == 1) {
                     // one MMA term: every warp stages its own slice of the biases and needs no block-wide
                     // barrier per tile (the warps drift apart freely)
                     float* cw = cn_s + (warp - 4) * kCols;
@@ -346,11 +395,12 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 for (int cc = 0; cc < kCols / 32; cc += 2) {
                     tmem_ld_wait_dep(ra);
                     tmem_ld_32x32(taddr + (cc + 1) * 32, rb);
-                    epi_chunk<SCORES, NPASS == 3>(ra, cn + cc * 32, off, cc * 32, p.pack_mask, te, to, score_row, kbase + cc * 32, p.K, inv_s);
+                    epi_chunk<SCORES, NPASS == 3, !AUG>(ra, cn + cc * 32, off, cc * 32, p.pack_mask, te, to, score_row,
+                                                        kbase + cc * 32, p.K, inv_s);
                     tmem_ld_wait_dep(rb);
                     if (cc + 2 < kCols / 32) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
-                    epi_chunk<SCORES, NPASS == 3>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32, p.pack_mask, te, to, score_row,
-                                      kbase + (cc + 1) * 32, p.K, inv_s);
+                    epi_chunk<SCORES, NPASS == 3, !AUG>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32, p.pack_mask, te, to,
+                                                        score_row, kbase + (cc + 1) * 32, p.K, inv_s);
                 }
                 tc_fence_before_sync();
                 __syncwarp();
@@ -458,6 +508,7 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
     KMC_TRY(make_map(fn, &c->tmap_xlo, c->at<void>(c->off_xlo), (uint64_t)c->D_pad, (uint64_t)c->n, kTcBlockM));
     KMC_TRY(make_map(fn, &c->tmap_c, c->at<void>(c->off_cplanes), (uint64_t)c->D_pad, (uint64_t)(2 * c->K_pad),
                      kTcBlockN));
+    KMC_TRY(make_map(fn, &c->tmap_bias, c->at<void>(c->off_cbias), (uint64_t)kTcChunkK, (uint64_t)c->K_pad, kTcBlockN));
     c->tmaps_ready = true;
     return 0;
 }
@@ -478,16 +529,24 @@ int launch_tc_gate(kmc_ctx* c, unsigned long long* amb_counter, unsigned int* fl
 
 template <int KC>
 static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s) {
-    auto kern = p.scores ? tc_assign_kernel<KC, true, 3, 8>
-                         : (terms == 1 ? tc_assign_kernel<KC, false, 1, 8> : tc_assign_kernel<KC, false, 3, 8>);
     const int threads = 128 + 32 * 8;
-    const uint32_t smem_bytes = (!p.scores && terms == 1) ? TcCfg<KC, 1>::kSmemBytes : TcCfg<KC, 3>::kSmemBytes;
-    KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int grid = p.n_mtiles < c->sm_count ? p.n_mtiles : c->sm_count;
-    kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, p);
-    KMC_CUDA(cudaGetLastError());
-    c->launches++;
-    return 0;
+    auto launch = [&](auto kern, uint32_t smem_bytes, const TcParams& pp) -> int {
+        KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, c->tmap_bias, pp);
+        KMC_CUDA(cudaGetLastError());
+        c->launches++;
+        return 0;
+    };
+    TcParams pp = p;
+    pp.use_bias_mma = 0;
+    if (p.scores) return launch(tc_assign_kernel<KC, true, 3, 8, false>, TcCfg<KC, 3>::kSmemBytes, pp);
+    if (terms != 1) return launch(tc_assign_kernel<KC, false, 3, 8, false>, TcCfg<KC, 3>::kSmemBytes, pp);
+    if (getenv("KMC_NO_BIAS_MMA")) return launch(tc_assign_kernel<KC, false, 1, 8, false>, TcCfg<KC, 1>::kSmemBytes, pp);
+    // one term: the variant that lets the MMA add the biases, and the plain one; the device runs exactly one
+    pp.use_bias_mma = 1;
+    KMC_TRY(launch(tc_assign_kernel<KC, false, 1, 8, true>, TcCfg<KC, 1>::kSmemBytes, pp));
+    return launch(tc_assign_kernel<KC, false, 1, 8, false>, TcCfg<KC, 1>::kSmemBytes, pp);
 }
 
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
@@ -514,6 +573,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.gamma = (float)c->tc_gamma;
     p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);
     p.pack_mask = 0xFFFFFF80u;
+    p.use_bias_mma = 0;
     if (!gate_flag) KMC_CUDA(cudaMemsetAsync(amb_counter, 0, sizeof(unsigned long long), s));
     switch ((int)(c->D_pad / kTcChunkK)) {
         case 1: return launch_tc_kc<1>(c, p, terms, s);

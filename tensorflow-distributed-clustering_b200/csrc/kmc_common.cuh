@@ -38,6 +38,11 @@ constexpr int kTcBlockM = 128;   // rows per tensor tile (TMEM lanes)
 constexpr int kTcBlockN = 256;   // centroids per tensor tile (TMEM columns of one accumulator)
 constexpr int kTcChunkK = 64;    // fp16 elements per 128-byte swizzle row
 constexpr int kStatSlots = 16;
+// score bias S*|c_k|^2 = sum_i kBiasConst[i] * piece_i with fp16 pieces (|piece| <= 65504): range 8.6e9,
+// resolution ~2^-10 absolute
+constexpr int kBiasPieces = 6;
+__device__ __constant__ const float kBiasConst[kBiasPieces] = {32768.f, 32768.f, 32768.f, 32768.f, 16.f, 0.0078125f};
+constexpr float kBiasMax = 2147483648.f;   // the plane is used only while max_k S*|c_k|^2 < 2^31
 constexpr int kMaxChunks = 4;    // row chunks of one accumulate pass (assign of chunk c+1 overlaps accumulate of chunk c)
 
 // Device-resident scalars written by kernels (all doubles / 64-bit so one memset clears them).
@@ -52,7 +57,7 @@ struct DeviceStats {
     float sigma_x;                    // power-of-two scale of the point planes
     float sigma_c;                    // power-of-two scale of the centroid planes (x -2 folded)
     unsigned int c_lonormmax_bits;    // max_k |C' - C'_hi| (scaled units): bound for the 1-term kernel
-    unsigned int pad0;
+    unsigned int cn_max_bits;         // max_k S*|c_k|^2 (fp32 bits): the bias plane is valid below 2^31
     unsigned int tc3_flag[kMaxChunks];      // set on the device when a 1-term pass certified too few rows of a chunk
 };
 
@@ -83,7 +88,7 @@ struct kmc_ctx {
     int64_t need_bytes = 0;
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_perm = 0,
             off_sort = 0, sort_stride = 0, sort_cursor = 0, sort_offsets = 0, sort_segoff = 0,
-            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0,
+            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0,
             off_ccdist = -1, off_nbr = -1;
     const float* points = nullptr;
     bool have_centroids = false;
@@ -92,6 +97,7 @@ struct kmc_ctx {
     alignas(64) CUtensorMap tmap_xhi;
     alignas(64) CUtensorMap tmap_xlo;
     alignas(64) CUtensorMap tmap_c;
+    alignas(64) CUtensorMap tmap_bias;
     bool tmaps_ready = false;
     // pinned staging
     void* pinned[2] = {nullptr, nullptr};

@@ -35,12 +35,13 @@ __device__ __forceinline__ float ld_stream_f1(const float* p) {
     return r;
 }
 
-// Power-of-two scale s such that absmax * s < 2^14 (fp16 range with headroom for the MMA).
+// Power-of-two scale s such that absmax * s < 2^12: far inside the fp16 range, and small enough that the
+// score biases S*|c|^2 fit the fp16 pieces of the bias plane (update.cu) for every D the tensor path takes.
 __host__ __device__ __forceinline__ float scale_from_absmax(float m) {
     if (!(m > 0.f) || !(m < 3.0e38f)) return 1.f;
     int e;
     frexpf(m, &e);                 // m = f * 2^e, f in [0.5, 1)
-    int sh = 14 - e;
+    int sh = 12 - e;
     sh = sh > 100 ? 100 : (sh < -100 ? -100 : sh);
     return ldexpf(1.f, sh);
 }

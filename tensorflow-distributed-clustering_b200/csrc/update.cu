@@ -81,7 +81,7 @@ int launch_centroid_absmax(kmc_ctx* c, cudaStream_t s) {
 __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __restrict__ cent, int K, int D,
                                                              int K_pad, int D_pad, __half* __restrict__ chi,
                                                              __half* __restrict__ clo, float* __restrict__ cnorm,
-                                                             DeviceStats* stats) {
+                                                             __half* __restrict__ cbias, DeviceStats* stats) {
     // 2*|c| < 2^14 after scaling: absmax of (2c)
     const float sigma_c = scale_from_absmax(2.f * __uint_as_float(stats->c_absmax_bits));
     const float sigma_x = stats->sigma_x;
@@ -120,6 +120,25 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
             ss_lo = fmaf(r, r, ss_lo);
         }
         ss_lo = warp_sum(ss_lo);
+        // bias plane: row k = fp16 pieces p_i with sum_i a_i * p_i = cn (a = kBiasConst), zero padded to one
+        // 64-column chunk; the tensor kernel multiplies it with a constant tile holding the a_i, so the MMA
+        // itself adds S*|c_k|^2 to every score.  Dead rows saturate (8.6e9, above every real score).
+        {
+            __half* br = cbias + (int64_t)k * kTcChunkK;
+            for (int j = lane; j < kTcChunkK; j += 32) br[j] = __float2half_rn(0.f);
+            __syncwarp();
+            if (lane == 0) {
+                double r = (double)cn;
+                for (int i = 0; i < kBiasPieces; ++i) {
+                    float q = dead ? ((i < 4) ? 65504.f : 0.f) : (float)(r / (double)kBiasConst[i]);
+                    q = fminf(fmaxf(q, -65504.f), 65504.f);
+                    const __half h = __float2half_rn(q);
+                    br[i] = h;
+                    r -= (double)kBiasConst[i] * (double)__half2float(h);
+                }
+                if (!dead) atomicMax(&stats->cn_max_bits, __float_as_uint(cn));
+            }
+        }
         if (lane == 0) {
             cnorm[k] = dead ? 3.0e38f : cn;
             if (!dead) {
@@ -138,11 +157,12 @@ int launch_prep_centroids(kmc_ctx* c, cudaStream_t s) {
     blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
     KMC_CUDA(cudaMemsetAsync(&c->stats()->c_normmax_bits, 0, sizeof(unsigned int), s));
     KMC_CUDA(cudaMemsetAsync(&c->stats()->c_lonormmax_bits, 0, sizeof(unsigned int), s));
+    KMC_CUDA(cudaMemsetAsync(&c->stats()->cn_max_bits, 0, sizeof(unsigned int), s));
     __half* chi = c->at<__half>(c->off_cplanes);
     __half* clo = chi + c->K_pad * c->D_pad;
     prep_centroids_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), (int)c->K, (int)c->D, (int)c->K_pad,
                                                            (int)c->D_pad, chi, clo, c->at<float>(c->off_cnorm),
-                                                           c->stats());
+                                                           c->at<__half>(c->off_cbias), c->stats());
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
