@@ -90,10 +90,21 @@ template <int KC, int NPASS> struct TcCfg {
 template <unsigned SLEEP_NS>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, DeviceStats* st, unsigned code) {
     if (mbar_try_wait(bar, parity)) return;
+    if (SLEEP_NS) {
+        // single-thread roles: parked by the hardware between polls (suspend-time hint), no clock reads
+        unsigned spins = 0;
+        while (!mbar_try_wait_hint(bar, parity, 4000u)) {
+            if (++spins > (1u << 22)) {        // >= 80 ms of polling (legitimate waits last microseconds): fail loudly
+                st->watchdog = code;
+                __threadfence_system();
+                __trap();
+            }
+        }
+        return;
+    }
     const long long t0 = clock64();
     unsigned spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (SLEEP_NS) __nanosleep(SLEEP_NS);
         if ((++spins & 1023u) == 0 && clock64() - t0 > 6000000000LL) {   // ~3 s: fail loudly, do not hang
             st->watchdog = code;
             __threadfence_system();
@@ -346,14 +357,19 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         const float cmax = __uint_as_float(p.stats->c_normmax_bits);
         const float clomax = __uint_as_float(p.stats->c_lonormmax_bits);
         uint32_t ac = 0;
+        // row norms of the NEXT row tile are fetched while the current one is scanned
+        auto tile_row = [&](int it) {
+            return ((int64_t)p.tile0 + blockIdx.x + (int64_t)it * gridDim.x) * kTcBlockM + q * 32 + lane;
+        };
+        float2 nn_next = make_float2(0.f, 0.f);
+        if (n_my_tiles > 0 && tile_row(0) < p.n) nn_next = *reinterpret_cast<const float2*>(p.xnorm + 2 * tile_row(0));
         for (int it = 0; it < n_my_tiles; ++it) {
-            const int64_t row = ((int64_t)p.tile0 + blockIdx.x + (int64_t)it * gridDim.x) * kTcBlockM + q * 32 + lane;
+            const int64_t row = tile_row(it);
             const bool row_ok = row < p.n;
-            float xn = 0.f, xlo = 0.f;
-            if (row_ok) {
-                const float2 nn = *reinterpret_cast<const float2*>(p.xnorm + 2 * row);
-                xn = nn.x; xlo = nn.y;
-            }
+            const float xn = nn_next.x, xlo = nn_next.y;
+            nn_next = make_float2(0.f, 0.f);
+            if (it + 1 < n_my_tiles && tile_row(it + 1) < p.n)
+                nn_next = *reinterpret_cast<const float2*>(p.xnorm + 2 * tile_row(it + 1));
             // certified if the two best scores are further apart than twice the score error bound:
             // 3 terms: operand split + accumulator truncation; 1 term: the dropped x_lo.c and x.c_lo too
             const float thr = (NPASS == 3) ? 2.f * p.gamma * xn * cmax

@@ -88,6 +88,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 
+// try_wait with a suspend-time hint: the hardware parks the thread until the phase completes or ~`ns`
+// elapse, so a waiting single-thread role costs its scheduler (shared with epilogue warps) almost no
+// issue slots.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity, uint32_t ns) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
+        "selp.b32 %0, 1, 0, P;\n\t}\n"
+        : "=r"(ok) : "r"(bar), "r"(parity), "r"(ns) : "memory");
+    return ok != 0;
+}
+
 // 2-D TMA tile load global -> shared, completion counted on an mbarrier.
 __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const void* tmap, int c0, int c1,
                                             uint32_t bar) {
