@@ -59,6 +59,10 @@ struct TcParams {
     float gamma1;        // accumulate error of the 1-term score
     int use_bias_mma;    // this launch is one of the AUG / plain pair: run only if AUG matches the device-side check
     uint32_t pack_mask;  // 0xFFFFFF80, see pack_idx
+    uint32_t blk_mask;   // ~(128 / kEpiG - 1): the packed block index of the partition epilogue
+    const float* x;      // fp32 points and centroids, D: exact distances of the rare rows whose best block
+    const float* cent;   // holds several cells within the packing truncation (see the partition epilogue)
+    int D;
 };
 
 // Shared-memory plan.  With one MMA term only the hi plane of the points is staged, which leaves
@@ -170,6 +174,85 @@ __device__ __forceinline__ void epi_chunk(const uint32_t (&r)[32], const float* 
             if (kbase + 4 * q + 3 < K) score_row[kbase + 4 * q + 3] = (v3 - off) * inv_s;
         }
     }
+}
+
+// ---- partition epilogue ---------------------------------------------------------------------------
+// Exact best / second-best of a row WITHOUT carrying an index through every score.  The columns a
+// thread scans are covered by two partitions in which any two columns share at most one cell:
+//   A: column mod G  -> G running minima over the whole row, raw scores, min3 chains (half an op per score)
+//   B: column div G  -> minimum of each block of G consecutive columns (half an op per score); only the
+//      block minima carry an index (block number in the low mantissa bits) through an exact top-2 chain.
+// The best score m1 is the smallest A cell (cell g*), its block h* comes from the best block minimum.  Every
+// other column lies outside cell g* or outside block h*, so
+//   second best = min( min_{g != g*} A_g , second-smallest block minimum )            (exact)
+// and the column of the best is h*·G + g*.  Cost: (1 + 2.5/G + 1/G) min/max/logic ops per score instead of
+// 3.5 (2.875 instead of 7 dispatch cycles at G = 8).  Equal or truncation-close candidates give
+// m2 - m1 <= pack error, i.e. an uncertified row that the exact refine decides.
+#ifndef KMC_EPI_G
+#define KMC_EPI_G 8
+#endif
+#ifdef KMC_EPI_OLD
+constexpr bool kOldEpi = true;
+#else
+constexpr bool kOldEpi = false;
+#endif
+constexpr int kEpiG = KMC_EPI_G;                    // 8 or 16
+constexpr int kEpiBlocksPerHalf = 128 / kEpiG;      // block numbers packed into the block minima
+constexpr float kBlkPackRel = (float)kEpiBlocksPerHalf * 1.3e-7f;   // > 2^-23 * blocks
+
+__device__ __forceinline__ float fmin3(float a, float b, float c) { return fminf(fminf(a, b), c); }
+
+// exact fp32 squared distance (difference form) of one row to one centroid; rare path, one thread per row
+__device__ __noinline__ float exact_dist_row(const float* __restrict__ x, const float* __restrict__ c, int D) {
+    float acc = 0.f;
+    for (int j = 0; j < D; ++j) {
+        const float d = x[j] - c[j];
+        acc = fmaf(d, d, acc);
+    }
+    return acc;
+}
+
+template <bool USE_OFF, bool USE_CN>
+__device__ __forceinline__ void epi_chunk_part(const uint32_t (&r)[32], const float* __restrict__ cn, float off,
+                                               int blk0, uint32_t mask, float (&ga)[kEpiG], Top2& tb) {
+    float v[32];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        v[4 * q + 0] = __uint_as_float(r[4 * q + 0]); v[4 * q + 1] = __uint_as_float(r[4 * q + 1]);
+        v[4 * q + 2] = __uint_as_float(r[4 * q + 2]); v[4 * q + 3] = __uint_as_float(r[4 * q + 3]);
+        if (USE_CN) {
+            const float4 c4 = *reinterpret_cast<const float4*>(cn + 4 * q);
+            v[4 * q + 0] += c4.x; v[4 * q + 1] += c4.y; v[4 * q + 2] += c4.z; v[4 * q + 3] += c4.w;
+        }
+        if (USE_OFF) { v[4 * q + 0] += off; v[4 * q + 1] += off; v[4 * q + 2] += off; v[4 * q + 3] += off; }
+    }
+    // partition A
+#pragma unroll
+    for (int g = 0; g < kEpiG; ++g) {
+        if (kEpiG == 8) {
+            ga[g] = fmin3(ga[g], v[g], v[8 + g]);
+            ga[g] = fmin3(ga[g], v[16 + g], v[24 + g]);
+        } else {
+            ga[g] = fmin3(ga[g], v[g], v[16 + g]);
+        }
+    }
+    // partition B
+    float bm[32 / kEpiG];
+#pragma unroll
+    for (int b = 0; b < 32 / kEpiG; ++b) {
+        const float* w = v + b * kEpiG;
+        float m;
+        if (kEpiG == 8) {
+            m = fminf(fmin3(w[0], w[1], w[2]), fmin3(fmin3(w[3], w[4], w[5]), w[6], w[7]));
+        } else {
+            const float t0 = fmin3(w[0], w[1], w[2]), t1 = fmin3(w[3], w[4], w[5]), t2 = fmin3(w[6], w[7], w[8]);
+            const float t3 = fmin3(w[9], w[10], w[11]), t4 = fmin3(w[12], w[13], w[14]);
+            m = fminf(fmin3(t0, t1, t2), fmin3(t3, t4, w[15]));
+        }
+        bm[b] = pack_idx(m, blk0 + b, mask);
+    }
+#pragma unroll
+    for (int b = 0; b < 32 / kEpiG; b += 2) top2_pair(tb, bm[b], bm[b + 1]);
 }
 
 template <int KC, bool SCORES, int NPASS, int EW, bool AUG>   // EW = epilogue warps; AUG = bias through the MMA
@@ -378,8 +461,13 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             // 2^-16 of a SMALL number; with 1 term the threshold is far above that truncation anyway
             const float off = (NPASS == 3) ? xn * xn * (sigma_c / sigma_x) : 0.f;
             float* score_row = (SCORES && p.scores && row_ok) ? p.scores + row * (int64_t)p.K : nullptr;
-            Top2 te = {INFINITY, INFINITY}, to = {INFINITY, INFINITY};
+            Top2 te = {INFINITY, INFINITY}, to = {INFINITY, INFINITY};     // SCORES (debug) build: per-score index
             int a_e = 0, a_o = 0;
+            float ga[kEpiG];                                                // partition epilogue
+#pragma unroll
+            for (int g = 0; g < kEpiG; ++g) ga[g] = INFINITY;
+            Top2 tb = {INFINITY, INFINITY};
+            int a_blk = 0;
             for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                 const uint32_t buf = ac & 1u;
                 const float* cn = cn_s;
@@ -403,7 +491,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 mbar_wait<0>(t_full(buf), (ac >> 1) & 1u, p.stats, 0x700u + buf);
                 tc_fence_after_sync();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kTcBlockN + half * kCols;
-                const float e_in = te.m1, o_in = to.m1;
+                const float e_in = te.m1, o_in = to.m1, b_in = tb.m1;
                 const int kbase = nt * kTcBlockN + half * kCols;
                 uint32_t ra[32], rb[32];
                 tmem_ld_32x32(taddr, ra);
@@ -411,12 +499,19 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 for (int cc = 0; cc < kCols / 32; cc += 2) {
                     tmem_ld_wait_dep(ra);
                     tmem_ld_32x32(taddr + (cc + 1) * 32, rb);
-                    epi_chunk<SCORES, NPASS == 3, !AUG>(ra, cn + cc * 32, off, cc * 32, p.pack_mask, te, to, score_row,
-                                                        kbase + cc * 32, p.K, inv_s);
+                    if constexpr (SCORES || kOldEpi)
+                        epi_chunk<SCORES, NPASS == 3, !AUG>(ra, cn + cc * 32, off, cc * 32, p.pack_mask, te, to, score_row,
+                                                            kbase + cc * 32, p.K, inv_s);
+                    else
+                        epi_chunk_part<NPASS == 3, !AUG>(ra, cn + cc * 32, off, cc * 32 / kEpiG, p.blk_mask, ga, tb);
                     tmem_ld_wait_dep(rb);
                     if (cc + 2 < kCols / 32) tmem_ld_32x32(taddr + (cc + 2) * 32, ra);
-                    epi_chunk<SCORES, NPASS == 3, !AUG>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32, p.pack_mask, te, to,
-                                                        score_row, kbase + (cc + 1) * 32, p.K, inv_s);
+                    if constexpr (SCORES || kOldEpi)
+                        epi_chunk<SCORES, NPASS == 3, !AUG>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32, p.pack_mask, te, to,
+                                                            score_row, kbase + (cc + 1) * 32, p.K, inv_s);
+                    else
+                        epi_chunk_part<NPASS == 3, !AUG>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32 / kEpiG, p.blk_mask,
+                                                         ga, tb);
                 }
                 tc_fence_before_sync();
                 __syncwarp();
@@ -424,12 +519,49 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 // a changed best value carries its column in the low bits
                 if (__float_as_uint(te.m1) != __float_as_uint(e_in)) a_e = kbase + (int)(__float_as_uint(te.m1) & 0x7Fu);
                 if (__float_as_uint(to.m1) != __float_as_uint(o_in)) a_o = kbase + (int)(__float_as_uint(to.m1) & 0x7Fu);
+                if (__float_as_uint(tb.m1) != __float_as_uint(b_in))
+                    a_blk = kbase + (int)(__float_as_uint(tb.m1) & (uint32_t)(kEpiBlocksPerHalf - 1)) * kEpiG;
             }
-            // merge the two chains of this thread ...
             float m1, m2;
             int a1;
-            if (to.m1 < te.m1) { m1 = to.m1; a1 = a_o; m2 = fminf(te.m1, to.m2); }
-            else { m1 = te.m1; a1 = a_e; m2 = fminf(to.m1, te.m2); }
+            if constexpr (SCORES || kOldEpi) {
+                // merge the two chains of this thread ...
+                if (to.m1 < te.m1) { m1 = to.m1; a1 = a_o; m2 = fminf(te.m1, to.m2); }
+                else { m1 = te.m1; a1 = a_e; m2 = fminf(to.m1, te.m2); }
+            } else {
+                // best = smallest A cell (lowest cell on ties); second best = the smaller of the best other A
+                // cell and the second-smallest block minimum
+                m1 = ga[0];
+#pragma unroll
+                for (int g = 1; g < kEpiG; ++g) m1 = fminf(m1, ga[g]);
+                int gr = 0;
+#pragma unroll
+                for (int g = kEpiG - 1; g >= 0; --g) gr = (ga[g] == m1) ? g : gr;
+                m2 = tb.m2;
+#pragma unroll
+                for (int g = 0; g < kEpiG; ++g) m2 = fminf(m2, (g == gr) ? INFINITY : ga[g]);
+                // Column of the best: block h' of the smallest PACKED block minimum, and the A cell whose
+                // minimum equals it up to the packing truncation.  The cell of that block's minimum always
+                // matches; when it is the only match the column is exact.  Several matches (an uncertified
+                // near tie, ~1e-4 of the rows) are resolved by exact distances of the matching columns of block
+                // h', so the refine never starts from a far-away centroid.
+                const uint32_t tbits = __float_as_uint(tb.m1) & p.blk_mask;
+                uint32_t hits = 0;
+#pragma unroll
+                for (int g = 0; g < kEpiG; ++g)
+                    hits |= ((__float_as_uint(ga[g]) & p.blk_mask) == tbits) ? (1u << g) : 0u;
+                a1 = a_blk + (hits ? __ffs(hits) - 1 : gr);
+                if ((hits & (hits - 1u)) != 0u && row_ok) {
+                    float bd = INFINITY;
+                    for (uint32_t h = hits; h; h &= h - 1u) {
+                        const int k = a_blk + __ffs(h) - 1;
+                        if (k < p.K) {
+                            const float d = exact_dist_row(p.x + row * p.D, p.cent + (int64_t)k * p.D, p.D);
+                            if (d < bd) { bd = d; a1 = k; }
+                        }
+                    }
+                }
+            }
             // ... and the column groups of the row through shared memory
             if (NPASS == 1 && kGroups == 2) {
                 // only the two warps that share a TMEM lane quarter meet, on their own named barrier
@@ -466,7 +598,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 if (row_ok) {
                     if (a1 >= p.K) a1 = 0;
                     p.labels[row] = a1;
-                    const float pack_err = kPackRel * (fabsf(m1) + fabsf(m2));
+                    const float pack_err = ((SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));
                     amb = p.worklist && (m2 - m1) <= thr + pack_err;
                 }
                 // one atomic per warp reserves the worklist slots of all its uncertified rows
@@ -589,6 +721,10 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.gamma = (float)c->tc_gamma;
     p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);
     p.pack_mask = 0xFFFFFF80u;
+    p.blk_mask = ~(uint32_t)(kEpiBlocksPerHalf - 1);
+    p.x = c->points;
+    p.cent = c->centroids();
+    p.D = (int)c->D;
     p.use_bias_mma = 0;
     if (!gate_flag) KMC_CUDA(cudaMemsetAsync(amb_counter, 0, sizeof(unsigned long long), s));
     switch ((int)(c->D_pad / kTcChunkK)) {
