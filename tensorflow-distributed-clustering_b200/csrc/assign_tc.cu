@@ -69,7 +69,10 @@ struct TcParams {
 // room on the SM for the CTAs of the accumulation kernels that run concurrently on the side stream.
 template <int KC, int NPASS> struct TcCfg {
     static constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
-    static constexpr int kStages = (KC == 1 && NPASS == 3) ? 4 : 3;
+#ifndef KMC_TC_STAGES1
+#define KMC_TC_STAGES1 3
+#endif
+    static constexpr int kStages = (NPASS == 1) ? KMC_TC_STAGES1 : ((KC == 1) ? 4 : 3);
     static constexpr uint32_t kBBytes = kStages * kStageBytesB;
     // 1 term: a constant 128 x 64 fp16 tile holding kBiasConst in its first columns; multiplied with a stage
     // of the bias plane it makes the MMA add S*|c_k|^2 to the accumulator (no FADD per score in the epilogue)
@@ -91,13 +94,16 @@ template <int KC, int NPASS> struct TcCfg {
 // Wait on an mbarrier phase.  The single-thread roles (producer, MMA issuer) share their scheduler
 // with epilogue warps, so a waiting thread backs off with nanosleep instead of spinning on the issue
 // slots the epilogue needs.  SLEEP_NS = 0 for the epilogue's own waits.
+#ifndef KMC_WAIT_HINT_NS
+#define KMC_WAIT_HINT_NS 4000u
+#endif
 template <unsigned SLEEP_NS>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, DeviceStats* st, unsigned code) {
     if (mbar_try_wait(bar, parity)) return;
     if (SLEEP_NS) {
         // single-thread roles: parked by the hardware between polls (suspend-time hint), no clock reads
         unsigned spins = 0;
-        while (!mbar_try_wait_hint(bar, parity, 4000u)) {
+        while (!mbar_try_wait_hint(bar, parity, KMC_WAIT_HINT_NS)) {
             if (++spins > (1u << 22)) {        // >= 80 ms of polling (legitimate waits last microseconds): fail loudly
                 st->watchdog = code;
                 __threadfence_system();
