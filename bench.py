@@ -418,7 +418,7 @@ def run_e2e(pkg, host, note, C0, D, K, steps, dev, world, n_total):
     out = {
         "value": total_rows * res["n_iter"] / dt, "unit": UNIT,
         "h2d_bytes_per_step": int(rows * D * 4 / max(steps, 1)),
-        "d2h_bytes_per_step": int((K * D * 4 + rows * 4) / max(steps, 1)),
+        "d2h_bytes_per_step": int((K * D * 4 + rows * 8) / max(steps, 1)),   # centroids fp32 + labels int64
         "rows": rows, "iterations": res["n_iter"], "seconds": dt,
         "initialization_time": res["initialization_time"], "computation_time": res["computation_time"],
         "inertia": res["inertia"],

@@ -160,6 +160,17 @@ int kmc_iterate(kmc_ctx* ctx, int max_iters, double tol, int* n_iter_out,
  */
 int kmc_assign(kmc_ctx* ctx, int32_t* dev_labels, void* stream);
 
+/*
+ * Deliver `n_labels` int32 device labels (as written by kmc_assign) to HOST memory as int32
+ * (label_bytes = 4) or int64 (label_bytes = 8: the dtype of the reference's `np.argmin(...)` result,
+ * :282; widened on the device).  `host_labels` may be pageable -- chunks are staged through the
+ * context's pinned double buffer and copied out by host threads while the next chunk is in flight -- or
+ * pinned (direct DMA).  Synchronises the stream.  Together with kmc_assign this replaces the reference's
+ * D2H of the whole N x K float64 distance matrix (:235, :255, :282).
+ */
+int kmc_labels_to_host(kmc_ctx* ctx, const int32_t* dev_labels, void* host_labels, int label_bytes,
+                       int64_t n_labels, void* stream);
+
 /* Synchronise `stream` and copy KMC_STAT_COUNT doubles (see KMC_STAT_*) to the host. */
 int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
 

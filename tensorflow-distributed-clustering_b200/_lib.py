@@ -46,6 +46,7 @@ SIGNATURES = {
     "kmc_update": (c_int, [c_void_p, c_void_p]),
     "kmc_iterate": (c_int, [c_void_p, c_int, c_double, POINTER(c_int), POINTER(c_double), POINTER(c_double), c_void_p]),
     "kmc_assign": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "kmc_labels_to_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "kmc_read_stats": (c_int, [c_void_p, POINTER(c_double), c_void_p]),
     "kmc_set_param": (c_int, [c_void_p, c_int, c_double]),
     "kmc_get_phase_ms": (c_int, [c_void_p, POINTER(c_float), c_int]),

@@ -161,6 +161,16 @@ class LloydShard:
             L.check(self.lib.kmc_assign(self._ctx, c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    def labels_to_host(self, dev_labels, out: np.ndarray) -> np.ndarray:
+        """Copy int32 device labels (from assign()) into the host array `out` (int32 or int64, contiguous):
+        widened on the device, staged through pinned buffers, no pinned allocation of the result."""
+        if out.dtype not in (np.int32, np.int64) or not out.flags.c_contiguous or out.shape != (dev_labels.numel(),):
+            raise ValueError("out must be a contiguous int32/int64 array with one entry per label")
+        with _torch().cuda.device(self.device):
+            L.check(self.lib.kmc_labels_to_host(self._ctx, c_void_p(dev_labels.data_ptr()), c_void_p(out.ctypes.data),
+                                                int(out.dtype.itemsize), int(out.shape[0]), self._stream()))
+        return out
+
     def stats(self) -> dict:
         buf = (c_double * L.KMC_STAT_COUNT)()
         with _torch().cuda.device(self.device):
@@ -386,14 +396,12 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     cluster_idx = None
     last_labels = None
     if return_labels:
-        # labels leave the GPU already widened to the reference's int64, straight into one pinned array
-        parts = [s.assign() for s in shards]
-        out = torch.empty(N, dtype=torch.int64, pin_memory=True)
-        for p, (r0, r1) in zip(parts, ranges):
-            out[r0:r1].copy_(p.to(torch.int64), non_blocking=True)
-        for s in shards:
-            torch.cuda.synchronize(s.device)
-        cluster_idx = out.numpy()
+        # labels leave the GPU already widened to the reference's int64, through the shard's pinned staging
+        # buffers into one ordinary array (no pinned allocation of N labels inside the call)
+        parts = [s.assign() for s in shards]                 # asynchronous on every GPU
+        cluster_idx = np.empty(N, dtype=np.int64)
+        for s, p, (r0, r1) in zip(shards, parts, ranges):
+            s.labels_to_host(p, cluster_idx[r0:r1])
         last_labels = cluster_idx[ranges[-1][0]:ranges[-1][1]]
     for s in shards:
         s.close()
@@ -461,12 +469,10 @@ class _OutOfCoreShard:
         return self.inner.stats()
 
     def assign_to_host(self, out):
-        """Labels of rows [r0, r1) into the pinned int64 tensor `out` (indexed by global row)."""
-        torch = _torch()
+        """Labels of rows [r0, r1) into the host int64 array `out` (indexed by global row)."""
         for b0, b1 in self._batches():
             self._load(b0, b1)
-            out[b0:b1].copy_(self.inner.assign().to(torch.int64), non_blocking=True)
-        torch.cuda.synchronize(self.device)
+            self.inner.labels_to_host(self.inner.assign(), out[b0:b1])
 
     def close(self):
         self.inner.close()
@@ -524,10 +530,7 @@ def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *,
     end_center = shard.get_centroids()
     labels = None
     if return_labels:
-        out = torch.empty(n_local, dtype=torch.int64, pin_memory=True)
-        out.copy_(shard.assign().to(torch.int64), non_blocking=True)
-        torch.cuda.synchronize(device)
-        labels = out.numpy()
+        labels = shard.labels_to_host(shard.assign(), np.empty(n_local, dtype=np.int64))
     shard.close()
     return {
         "end_center": end_center, "cluster_idx": labels, "centroids": labels, "init_center": init_center,
@@ -562,10 +565,9 @@ def _k_means_out_of_core(data, K, dev_ids, ranges, init_center, n_max_iters, bat
     end_center = shards[0].get_centroids()
     cluster_idx = last_labels = None
     if return_labels:
-        out = torch.empty(N, dtype=torch.int64, pin_memory=True)
+        cluster_idx = np.empty(N, dtype=np.int64)
         for s in shards:
-            s.assign_to_host(out)
-        cluster_idx = out.numpy()
+            s.assign_to_host(cluster_idx)
         last_labels = cluster_idx[ranges[-1][0]:ranges[-1][1]]
     for s in shards:
         s.close()

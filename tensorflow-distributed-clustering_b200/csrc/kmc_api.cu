@@ -147,7 +147,7 @@ static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -
 }
 
 static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
-    const size_t kMin = (size_t)8 << 20;
+    const size_t kMin = (size_t)2 << 20;
     if (bytes < 2 * kMin) { memcpy(dst, src, bytes); return; }
     unsigned nt = std::thread::hardware_concurrency();
     nt = nt == 0 ? 1 : (nt > 8 ? 8 : nt);
@@ -166,6 +166,26 @@ static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
 }  // namespace kmc
 
 using namespace kmc;
+
+// pinned double buffer (and, for conversions on the device, two device buffers) of the staging paths;
+// sized on first use (H2D of pageable rows: 64 MB chunks for the host copy threads; labels D2H: 16 MB)
+static const int64_t kStageChunk = (int64_t)64 << 20;    // bytes per buffer, row staging
+static const int64_t kLabelChunk = (int64_t)16 << 20;    // bytes per buffer, label delivery
+
+static int ensure_staging(kmc_ctx* c, int64_t bytes, bool need_dev) {
+    if (c->stage_bytes < bytes) {
+        for (int i = 0; i < 2; ++i) {
+            if (c->pinned[i]) { KMC_CUDA(cudaFreeHost(c->pinned[i])); c->pinned[i] = nullptr; }
+            if (c->dev_stage[i]) { KMC_CUDA(cudaFree(c->dev_stage[i])); c->dev_stage[i] = nullptr; }
+            KMC_CUDA(cudaHostAlloc(&c->pinned[i], (size_t)bytes, cudaHostAllocDefault));
+            if (!c->pinned_free[i]) KMC_CUDA(cudaEventCreateWithFlags(&c->pinned_free[i], cudaEventDisableTiming));
+        }
+        c->stage_bytes = bytes;
+    }
+    if (need_dev && !c->dev_stage[0])
+        for (int i = 0; i < 2; ++i) KMC_CUDA(cudaMalloc(&c->dev_stage[i], (size_t)c->stage_bytes));
+    return 0;
+}
 
 extern "C" {
 
@@ -319,17 +339,8 @@ int kmc_stage_points(kmc_ctx* c, float* dev_dst, const void* host_src, int src_d
         KMC_CUDA(cudaStreamSynchronize(s));
         return 0;
     }
-    const int64_t kChunk = (int64_t)64 << 20;   // bytes per pinned buffer
-    if (!c->pinned[0]) {
-        for (int i = 0; i < 2; ++i) {
-            KMC_CUDA(cudaHostAlloc(&c->pinned[i], (size_t)kChunk, cudaHostAllocDefault));
-            KMC_CUDA(cudaEventCreateWithFlags(&c->pinned_free[i], cudaEventDisableTiming));
-        }
-        c->stage_bytes = kChunk;
-    }
-    if (src_dtype == KMC_DTYPE_F64 && !c->dev_stage[0]) {
-        for (int i = 0; i < 2; ++i) KMC_CUDA(cudaMalloc(&c->dev_stage[i], (size_t)kChunk));
-    }
+    const int64_t kChunk = kStageChunk;
+    KMC_TRY(ensure_staging(c, kStageChunk, src_dtype == KMC_DTYPE_F64));
     const int64_t elems_per_chunk = kChunk / (int64_t)esz;
     int b = 0;
     for (int64_t e0 = 0; e0 < count; e0 += elems_per_chunk, b ^= 1) {
@@ -521,6 +532,53 @@ int kmc_assign(kmc_ctx* c, int32_t* dev_labels, void* stream) {
     if (c->n == 0) return 0;
     KMC_CUDA(cudaSetDevice(c->device));
     return assign_into(c, dev_labels, static_cast<cudaStream_t>(stream));
+}
+
+int kmc_labels_to_host(kmc_ctx* c, const int32_t* dev_labels, void* host_labels, int label_bytes, int64_t n_labels,
+                       void* stream) {
+    if (!c || (n_labels > 0 && (!dev_labels || !host_labels))) KMC_FAIL(KMC_E_INVALID, "null argument");
+    if (label_bytes != 4 && label_bytes != 8) KMC_FAIL(KMC_E_INVALID, "label_bytes must be 4 or 8, not %d", label_bytes);
+    if (n_labels <= 0) return 0;
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    cudaPointerAttributes attr;
+    bool dst_pinned = false;
+    if (cudaPointerGetAttributes(&attr, host_labels) == cudaSuccess) dst_pinned = (attr.type == cudaMemoryTypeHost);
+    cudaGetLastError();
+    char* dst = static_cast<char*>(host_labels);
+    if (dst_pinned && label_bytes == 4) {
+        KMC_CUDA(cudaMemcpyAsync(dst, dev_labels, (size_t)n_labels * 4, cudaMemcpyDeviceToHost, s));
+        KMC_CUDA(cudaStreamSynchronize(s));
+        return 0;
+    }
+    KMC_TRY(ensure_staging(c, kLabelChunk, label_bytes == 8));
+    const int64_t per = kLabelChunk / label_bytes;        // labels per chunk
+    const int64_t n_chunks = (n_labels + per - 1) / per;
+    auto chunk_len = [&](int64_t i) { return (i + 1) * per <= n_labels ? per : n_labels - i * per; };
+    for (int64_t i = 0; i <= n_chunks; ++i) {
+        const int b = (int)(i & 1);
+        if (i < n_chunks) {
+            // chunk i: (widen on the device,) copy to the pinned buffer -- or straight into a pinned destination
+            const int64_t r0 = i * per, nr = chunk_len(i);
+            const void* src = dev_labels + r0;
+            if (label_bytes == 8) {
+                KMC_TRY(launch_widen_labels(dev_labels + r0, static_cast<long long*>(c->dev_stage[b]), nr, s));
+                c->launches++;
+                src = c->dev_stage[b];
+            }
+            void* to = dst_pinned ? (void*)(dst + (size_t)r0 * label_bytes) : c->pinned[b];
+            KMC_CUDA(cudaMemcpyAsync(to, src, (size_t)nr * label_bytes, cudaMemcpyDeviceToHost, s));
+            KMC_CUDA(cudaEventRecord(c->pinned_free[b], s));
+        }
+        if (i > 0 && !dst_pinned) {
+            // chunk i-1 has landed: the host copies it out while chunk i is in flight
+            const int pb = b ^ 1;
+            KMC_CUDA(cudaEventSynchronize(c->pinned_free[pb]));
+            parallel_memcpy(dst + (size_t)(i - 1) * per * label_bytes, c->pinned[pb], (size_t)chunk_len(i - 1) * label_bytes);
+        }
+    }
+    KMC_CUDA(cudaStreamSynchronize(s));
+    return 0;
 }
 
 int kmc_set_param(kmc_ctx* c, int param, double value) {

@@ -24,6 +24,23 @@ int launch_convert_f64(const double* src, float* dst, int64_t count, cudaStream_
     return 0;
 }
 
+// int32 labels -> int64 (the dtype of the reference's np.argmin result), on the device so that the host
+// only copies
+__global__ void __launch_bounds__(256) widen_labels_kernel(const int32_t* __restrict__ src, long long* __restrict__ dst,
+                                                           int64_t count) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) dst[i] = (long long)src[i];
+}
+
+int launch_widen_labels(const int32_t* src, long long* dst, int64_t count, cudaStream_t s) {
+    if (count <= 0) return 0;
+    int64_t blocks = (count + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    widen_labels_kernel<<<(unsigned)blocks, 256, 0, s>>>(src, dst, count);
+    KMC_CUDA(cudaGetLastError());
+    return 0;
+}
+
 // max |x| over a flat fp32 array (NaNs ignored), folded into *out_bits with atomicMax on the
 // bit pattern (non-negative floats order like unsigned ints).
 __global__ void __launch_bounds__(256) absmax_kernel(const float* __restrict__ x, int64_t count,

@@ -218,6 +218,27 @@ def test_host_staging_fp64_fp32_and_batches(pkg, cuda_device):
             s.close()
 
 
+def test_labels_to_host_int32_int64_pageable_and_pinned(pkg, cuda_device):
+    """kmc_labels_to_host: several staging chunks (> 16 MB of labels), both widths, pageable and pinned targets."""
+    import torch
+
+    n = 5_000_011                                    # 40 MB of int64 labels: three chunks, ragged tail
+    X, _ = pkg.datagen.blobs_numpy(n, 2, 8, seed=5)
+    s = _shard(pkg, X, 8, cuda_device)
+    s.set_centroids(X[:8])
+    dev = s.assign()
+    want = dev.cpu().numpy()
+    for dt in (np.int32, np.int64):
+        out = s.labels_to_host(dev, np.full(n, -7, dtype=dt))
+        assert out.dtype == dt and np.array_equal(out, want)
+        pinned = torch.empty(n, dtype=torch.int32 if dt == np.int32 else torch.int64, pin_memory=True)
+        s.labels_to_host(dev, pinned.numpy())
+        assert np.array_equal(pinned.numpy(), want)
+    with pytest.raises(ValueError):
+        s.labels_to_host(dev, np.empty(n, dtype=np.int16))
+    s.close()
+
+
 def test_drop_in_entry_point_matches_oracle(pkg, cuda_device):
     X, _ = pkg.datagen.blobs_numpy(20000, 2, 8, seed=123128)
     X64 = X.astype(np.float64)                       # the reference feeds float64 (make_classification)
