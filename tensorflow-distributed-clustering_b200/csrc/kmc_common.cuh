@@ -59,6 +59,10 @@ struct DeviceStats {
     unsigned int c_lonormmax_bits;    // max_k |C' - C'_hi| (scaled units): bound for the 1-term kernel
     unsigned int cn_max_bits;         // max_k S*|c_k|^2 (fp32 bits): the bias plane is valid below 2^31
     unsigned int tc3_flag[kMaxChunks];      // set on the device when a 1-term pass certified too few rows of a chunk
+    // exact distances evaluated / rows handled by the last two refine launches (slot = launch parity): the next
+    // launch reads the previous slot to pick the kernel that fits the walk lengths (see refine.cu)
+    unsigned long long walk_sum[2];
+    unsigned long long walk_rows[2];
 };
 
 }  // namespace kmc
@@ -82,6 +86,7 @@ struct kmc_ctx {
     cudaEvent_t side_done = nullptr, side_go = nullptr;
     cudaEvent_t amb_event = nullptr;
     bool amb_pending = false;
+    unsigned int refine_launches = 0;   // parity selects the walk-statistics slot of DeviceStats
     // workspace
     char* ws = nullptr;
     int64_t ws_bytes = 0;

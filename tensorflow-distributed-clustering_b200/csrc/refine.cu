@@ -10,6 +10,7 @@
 // Part of the replacement of reference scripts/distribuitedClustering.py:221-234.
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
+#include <cstdlib>
 
 namespace kmc {
 
@@ -154,18 +155,30 @@ refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent
 // (8 lanes per candidate, each lane a strided set of float4 slices of the row), starting with the first
 // four entries of the anchor's list (entry 0 is the anchor itself), so the usual row -- anchor plus one
 // or two siblings inside the pruning radius -- costs one batch.
+// Walk-length feedback: every refine launch records how many exact distances it evaluated per row; the next
+// launch (both kernels are enqueued, one returns at once) runs the warp-per-row kernel when the previous walks
+// were long (far-from-converged centroids: hundreds of candidates inside the pruning radius) and the
+// 8-lanes-per-row kernel when they were short (converged blobs: two candidates).  Unknown (first launch) = long.
+__device__ __forceinline__ bool long_walks_expected(const DeviceStats* stats, int prev_slot) {
+    const unsigned long long r = stats->walk_rows[prev_slot], s = stats->walk_sum[prev_slot];
+    return r == 0ull || s > 6ull * r;
+}
+
 template <int NV>   // float4 slices per lane: D <= 32 * NV * 4 / 4 ... lane t owns float4 indices t, t+8, ...
 __global__ void __launch_bounds__(256)
 refine4_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
                const float* __restrict__ cc, const int32_t* __restrict__ nbr,
                const int32_t* __restrict__ worklist, const unsigned long long* __restrict__ n_work_dev,
-               int32_t* __restrict__ labels) {
+               int32_t* __restrict__ labels, DeviceStats* __restrict__ stats, int slot, int select) {
+    if (select && !long_walks_expected(stats, slot ^ 1)) return;      // refine8_kernel runs this launch instead
     const int lane = threadIdx.x & 31, g = lane >> 3, t = lane & 7;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t n_work = (int64_t)(*n_work_dev);
     const int nvec = D >> 2;
+    unsigned long long walked = 0, rows_done = 0;
     for (int64_t w = warp; w < n_work; w += nwarps) {
+        ++rows_done;
         const int64_t row = worklist[w];
         const int a = labels[row];
         float4 xr[NV];
@@ -215,10 +228,120 @@ refine4_kernel(const float* __restrict__ x, int D, const float* __restrict__ cen
                 if (od < d || (od == d && ok < kk)) { d = od; kk = ok; }
             }
             if (d < best || (d == best && kk < bk)) { best = d; bk = kk; }
+            walked += 4;
             // sorted: once an entry of this batch is outside the radius, all later ones are
             if (__ballot_sync(0xffffffffu, !(ccv < lim)) != 0u) break;
         }
         if (lane == 0) labels[row] = (bk == 0x7fffffff) ? a : bk;
+    }
+    if (lane == 0 && rows_done) {
+        atomicAdd(&stats->walk_sum[slot], walked);
+        atomicAdd(&stats->walk_rows[slot], rows_done);
+    }
+}
+
+// Eight lanes per row, four rows per warp.  Most uncertified rows need two exact distances (the tensor
+// kernel's pick and the centroid sharing its blob): entries 0 and 1 of the anchor's sorted list are evaluated
+// together, then the walk continues four entries per step (independent accumulators, each predicated on the
+// pruning radius) until the first entry outside the radius.  Same pruning rule, same lexicographic
+// (distance, index) argmin and the same walk order as refine4_kernel, which spends a whole warp on one row.
+template <int NV>
+__device__ __forceinline__ float group_dist(const float4 (&xr)[NV], const float* __restrict__ cent, int k, int D,
+                                            int nvec, int t) {
+    float acc = 0.f;
+    if (k >= 0) {
+        const float4* cp = reinterpret_cast<const float4*>(cent + (int64_t)k * D);
+#pragma unroll
+        for (int q = 0; q < NV; ++q) {
+            const int v = t + 8 * q;
+            if (v < nvec) {
+                const float4 cv = cp[v];
+                const float d0 = xr[q].x - cv.x, d1 = xr[q].y - cv.y, d2 = xr[q].z - cv.z, d3 = xr[q].w - cv.w;
+                acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+            }
+        }
+    }
+    return acc;
+}
+
+__device__ __forceinline__ float group_sum8(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    return v;
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256)
+refine8_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
+               const float* __restrict__ cc, const int32_t* __restrict__ nbr,
+               const int32_t* __restrict__ worklist, const unsigned long long* __restrict__ n_work_dev,
+               int32_t* __restrict__ labels, DeviceStats* __restrict__ stats, int slot, int select) {
+    if (select && long_walks_expected(stats, slot ^ 1)) return;       // refine4_kernel runs this launch instead
+    const int lane = threadIdx.x & 31, g = lane >> 3, t = lane & 7;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t n_work = (int64_t)(*n_work_dev);
+    const int nvec = D >> 2;
+    unsigned long long walked = 0, rows_done = 0;
+    for (int64_t w0 = warp * 4; w0 < n_work; w0 += nwarps * 4) {
+        const int64_t w = w0 + g;
+        const bool live = w < n_work;
+        if (live) { ++rows_done; walked += 2; }
+        const int64_t row = live ? worklist[w] : 0;
+        const int a = live ? labels[row] : 0;
+        float4 xr[NV];
+        const float4* xp = reinterpret_cast<const float4*>(x + row * D);
+#pragma unroll
+        for (int q = 0; q < NV; ++q) {
+            const int v = t + 8 * q;
+            xr[q] = (live && v < nvec) ? ld_stream_f4(xp + v) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const float* ccrow = cc + (int64_t)a * K;
+        const int32_t* nbrow = nbr + (int64_t)a * K;
+        float best = INFINITY, lim = INFINITY;
+        int bk = 0x7fffffff;
+        auto take = [&](float d, int k) {
+            if (k >= 0 && (d < best || (d == best && k < bk))) { best = d; bk = k; }
+        };
+        // entries 0 (the anchor, or an identical centroid: its distance sets the pruning radius) and 1
+        const int k0 = live ? nbrow[0] : -1;
+        const int k1 = (live && K > 1) ? nbrow[1] : -1;
+        const float c1 = (live && K > 1) ? ccrow[1] : INFINITY;
+        const float c2 = (live && K > 2) ? ccrow[2] : INFINITY;
+        float d0 = group_dist<NV>(xr, cent, k0, D, nvec, t);
+        float d1 = group_dist<NV>(xr, cent, k1, D, nvec, t);
+        d0 = group_sum8(d0);
+        d1 = group_sum8(d1);
+        if (live) lim = 4.f * d0 * 1.0001f + 1e-30f;
+        take(d0, k0);
+        if (c1 < lim) take(d1, k1);
+        // sorted list: the first entry outside the radius ends the walk
+        bool active = live && (c1 < lim) && (c2 < lim);
+        for (int j = 2; __any_sync(0xffffffffu, active); j += 4) {
+            int kk[4];
+            bool inside = true;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int ju = j + u;
+                inside = inside && active && ju < K && (ccrow[ju] < lim);
+                kk[u] = inside ? nbrow[ju] : -1;
+            }
+            float dd[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) dd[u] = group_dist<NV>(xr, cent, kk[u], D, nvec, t);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) dd[u] = group_sum8(dd[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) take(dd[u], kk[u]);
+            if (active) walked += 4;
+            active = inside;
+        }
+        if (live && t == 0) labels[row] = (bk == 0x7fffffff) ? a : bk;
+    }
+    if (t == 0 && rows_done) {
+        atomicAdd(&stats->walk_sum[slot], walked);
+        atomicAdd(&stats->walk_rows[slot], rows_done);
     }
 }
 
@@ -231,9 +354,21 @@ int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const un
     const int32_t* nbr = sorted ? c->at<int32_t>(c->off_nbr) : nullptr;
     if (sorted && c->D % 4 == 0 && c->D <= 256 && ((reinterpret_cast<uintptr_t>(c->points) & 15) == 0)) {
         const int nv = (int)((c->D / 4 + 7) / 8);
+        // KMC_REFINE_KERNEL=4 | 8 pins one kernel (A/B runs); default: both enqueued, the device picks
+        static const int pin = getenv("KMC_REFINE_KERNEL") ? atoi(getenv("KMC_REFINE_KERNEL")) : 0;
+        const int slot = (int)(c->refine_launches++ & 1u);
+        KMC_CUDA(cudaMemsetAsync(&c->stats()->walk_sum[slot], 0, sizeof(unsigned long long), s));
+        KMC_CUDA(cudaMemsetAsync(&c->stats()->walk_rows[slot], 0, sizeof(unsigned long long), s));
 #define KMC_REFINE4(N)                                                                                          \
-    refine4_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, nbr, worklist, nw, \
-                                             labels)
+    do {                                                                                                        \
+        if (pin != 8)                                                                                           \
+            refine4_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, nbr,  \
+                                                     worklist, nw, labels, c->stats(), slot, pin == 0);        \
+        if (pin != 4)                                                                                           \
+            refine8_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, nbr,  \
+                                                     worklist, nw, labels, c->stats(), slot, pin == 0);        \
+        c->launches += (pin == 0);                                                                              \
+    } while (0)
         if (nv <= 1) KMC_REFINE4(1);
         else if (nv <= 2) KMC_REFINE4(2);
         else if (nv <= 4) KMC_REFINE4(4);
