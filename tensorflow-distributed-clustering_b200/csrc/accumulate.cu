@@ -135,8 +135,13 @@ template <> struct RowVec<1> {
 // run: it reads 32 permutation entries with one coalesced load, then keeps 8/P rows (512 B each at
 // D=128) in flight per lane group before folding them into fp32 accumulators -- the gather is
 // latency-bound, so bytes in flight per SM are what sets the bandwidth.
+#ifdef KMC_SEGSUM_MAXNREG
+#define KMC_SEGSUM_ATTR __maxnreg__(KMC_SEGSUM_MAXNREG)
+#else
+#define KMC_SEGSUM_ATTR __launch_bounds__(256)
+#endif
 template <int VEC, int P>
-__global__ void __launch_bounds__(256)
+__global__ void KMC_SEGSUM_ATTR
 segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict__ cent,
               const int32_t* __restrict__ perm, const unsigned int* __restrict__ offsets,
               const unsigned int* __restrict__ segoff, double* __restrict__ partials, int lpr_log2) {

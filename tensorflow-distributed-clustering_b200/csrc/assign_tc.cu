@@ -262,7 +262,10 @@ __device__ __forceinline__ void epi_chunk_part(const uint32_t (&r)[32], const fl
 }
 
 template <int KC, bool SCORES, int NPASS, int EW, bool AUG>   // EW = epilogue warps; AUG = bias through the MMA
-__global__ void __maxnreg__(128)
+#ifndef KMC_TC_MAXNREG
+#define KMC_TC_MAXNREG 128
+#endif
+__global__ void __maxnreg__(SCORES ? 128 : KMC_TC_MAXNREG)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_bias,
                  const TcParams p) {

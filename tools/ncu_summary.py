@@ -50,8 +50,8 @@ def full(path):
                 print(f"  {k:86s} {rec[k]:>16s} {units[hdr.index(k)]}")
         rd, wr = rec.get("dram__bytes_read.sum"), rec.get("dram__bytes_write.sum")
         if rd and wr:
-            u = units[hdr.index("dram__bytes_read.sum")]
-            print(f"  dram traffic (read+write)  {rd} + {wr} {u}")
+            ur, uw = units[hdr.index("dram__bytes_read.sum")], units[hdr.index("dram__bytes_write.sum")]
+            print(f"  dram traffic (read + write)  {rd} {ur} + {wr} {uw}")
 
 
 if __name__ == "__main__":
