@@ -181,6 +181,9 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
                                    uncertified row; 3 = fp32-accurate split; 0 (default) = start with 1 where
                                    that pays off and fall back to 3 if too many rows need the refine */
 #define KMC_PARAM_PROFILE   2   /* non-zero: record CUDA events around each phase (see below) */
+#define KMC_PARAM_REFINE_KERNEL 4 /* exact refine of uncertified rows: 4 = warp per row (long candidate walks),
+                                   8 = eight lanes per row (short walks), 0 (default) = both enqueued, the
+                                   device picks from the walk lengths of the previous launch */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 
 /*

@@ -593,6 +593,10 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             c->tc_terms = (int)value;
             c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->off_nbr >= 0) ? 1 : 3);
             return 0;
+        case KMC_PARAM_REFINE_KERNEL:
+            if (value != 0.0 && value != 4.0 && value != 8.0) KMC_FAIL(KMC_E_INVALID, "refine kernel must be 0, 4 or 8");
+            c->refine_kernel = (int)value;
+            return 0;
         case KMC_PARAM_PROFILE:
             c->profile = value != 0.0;
             c->prof_acc_n = c->prof_upd_n = 0;

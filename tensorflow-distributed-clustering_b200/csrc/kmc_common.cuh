@@ -86,6 +86,7 @@ struct kmc_ctx {
     cudaEvent_t side_done = nullptr, side_go = nullptr;
     cudaEvent_t amb_event = nullptr;
     bool amb_pending = false;
+    int refine_kernel = 0;              // KMC_PARAM_REFINE_KERNEL: 0 = picked on the device, 4 or 8 = fixed
     unsigned int refine_launches = 0;   // parity selects the walk-statistics slot of DeviceStats
     // workspace
     char* ws = nullptr;

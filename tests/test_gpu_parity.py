@@ -218,6 +218,28 @@ def test_host_staging_fp64_fp32_and_batches(pkg, cuda_device):
             s.close()
 
 
+@pytest.mark.parametrize("kernel", [0, 4, 8])
+def test_refine_kernels_agree_with_the_oracle_on_long_and_short_walks(kernel, pkg, cuda_device):
+    """Both exact-refine kernels (warp per row / 8 lanes per row) and the on-device choice between them:
+    iteration 1 from C0 = X[0:K] has long candidate walks (blobs without a centroid), later ones short."""
+    X, _ = pkg.datagen.blobs_numpy(60000, 64, 96, seed=11)
+    C0 = X[:96].copy()
+    s = _shard(pkg, X, 96, cuda_device, path="tc")
+    s.set_centroids(C0)
+    s.set_param(pkg._lib.KMC_PARAM_TC_TERMS, 1)            # every uncertified row goes through the refine
+    s.set_param(pkg._lib.KMC_PARAM_REFINE_KERNEL, kernel)
+    C = C0.astype(np.float64)
+    for it in range(4):
+        lab = s.assign().cpu().numpy()
+        ref, d1, d2 = oracle.assign(X, C)
+        assert len(oracle.label_mismatches(lab, ref, d1, d2, TIE_RTOL)) == 0, f"iteration {it}"
+        s.accumulate()
+        s.update()
+        C = s.get_centroids().astype(np.float64)
+    assert s.stats()["ambiguous"] > 0
+    s.close()
+
+
 def test_labels_to_host_int32_int64_pageable_and_pinned(pkg, cuda_device):
     """kmc_labels_to_host: several staging chunks (> 16 MB of labels), both widths, pageable and pinned targets."""
     import torch
