@@ -307,6 +307,17 @@ def _as_host_matrix(data_batch):
     return np.ascontiguousarray(arr)
 
 
+def _prefaulted_labels(n: int):
+    """The int64 label array the call returns, with its pages touched by a helper thread while the GPUs
+    work (a fresh 8n-byte array costs one page fault per 4 KB on first write; numpy releases the GIL)."""
+    import threading
+
+    out = np.empty(int(n), dtype=np.int64)
+    th = threading.Thread(target=out.fill, args=(0,), daemon=True)
+    th.start()
+    return out, th
+
+
 def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_iters=20, *,
                          seed=None, batch_size=None, tol=0.0, empty="keep", path="auto",
                          return_labels=True, out_of_core=None):
@@ -364,6 +375,7 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
                                     return_labels, setup_ts)
     shards = [LloydShard(r1 - r0, D, K, torch.device("cuda", dev), empty=empty, path=path)
               for dev, (r0, r1) in zip(dev_ids, ranges)]
+    cluster_idx, toucher = _prefaulted_labels(N) if return_labels else (None, None)
     setup_time = float(time.time() - setup_ts)
 
     # ---- initialisation: H2D of every shard + centroids (:272-274) ----
@@ -393,13 +405,12 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
 
     # ---- label pass against the updated centroids (:255, :282) ----
     end_center = shards[0].get_centroids()
-    cluster_idx = None
     last_labels = None
     if return_labels:
         # labels leave the GPU already widened to the reference's int64, through the shard's pinned staging
         # buffers into one ordinary array (no pinned allocation of N labels inside the call)
         parts = [s.assign() for s in shards]                 # asynchronous on every GPU
-        cluster_idx = np.empty(N, dtype=np.int64)
+        toucher.join()
         for s, p, (r0, r1) in zip(shards, parts, ranges):
             s.labels_to_host(p, cluster_idx[r0:r1])
         last_labels = cluster_idx[ranges[-1][0]:ranges[-1][1]]
@@ -509,6 +520,7 @@ def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *,
     n_local, D = int(rows.shape[0]), int(rows.shape[1])
     init_center = np.array(initial_centers, dtype=np.float32, copy=True)
     shard = LloydShard(n_local, D, int(K), device, empty=empty, path=path)
+    labels, toucher = _prefaulted_labels(n_local) if return_labels else (None, None)
     setup_time = float(time.time() - setup_ts)
 
     initialization_ts = time.time()
@@ -528,9 +540,10 @@ def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *,
     computation_time = float(time.time() - aux_ts)
 
     end_center = shard.get_centroids()
-    labels = None
     if return_labels:
-        labels = shard.labels_to_host(shard.assign(), np.empty(n_local, dtype=np.int64))
+        dev_labels = shard.assign()
+        toucher.join()
+        shard.labels_to_host(dev_labels, labels)
     shard.close()
     return {
         "end_center": end_center, "cluster_idx": labels, "centroids": labels, "init_center": init_center,

@@ -218,6 +218,22 @@ def test_host_staging_fp64_fp32_and_batches(pkg, cuda_device):
             s.close()
 
 
+@pytest.mark.parametrize("terms", [1, 3])
+def test_well_separated_rows_are_certified_by_the_tensor_kernel(terms, pkg, cuda_device):
+    """Guards the epilogue's best / second-best bookkeeping: on blobs with one centroid each nearly every row
+    must be certified by the tensor kernel itself (a wrong second-best would flood or starve the refine)."""
+    k = 256
+    X, centers = pkg.datagen.blobs_numpy(40000, 128, k, seed=21)
+    s = _shard(pkg, X, k, cuda_device, path="tc")
+    s.set_centroids(centers.astype(np.float32))
+    s.set_param(pkg._lib.KMC_PARAM_TC_TERMS, terms)
+    lab = s.assign().cpu().numpy()
+    ref, d1, d2 = oracle.assign(X, centers.astype(np.float32))
+    assert len(oracle.label_mismatches(lab, ref, d1, d2, TIE_RTOL)) == 0
+    assert s.stats()["ambiguous"] <= 0.002 * X.shape[0], s.stats()
+    s.close()
+
+
 @pytest.mark.parametrize("kernel", [0, 4, 8])
 def test_refine_kernels_agree_with_the_oracle_on_long_and_short_walks(kernel, pkg, cuda_device):
     """Both exact-refine kernels (warp per row / 8 lanes per row) and the on-device choice between them:
