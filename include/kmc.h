@@ -58,6 +58,8 @@ typedef struct kmc_ctx kmc_ctx;
 #define KMC_STAT_AMBIGUOUS   2  /* rows the tensor path sent to the exact refine kernel, last pass */
 #define KMC_STAT_KERNEL_PATH 3  /* KMC_PATH_* actually used */
 #define KMC_STAT_LAUNCHES    4  /* kernels launched by this ctx since creation */
+#define KMC_STAT_X_SCALED_MAX 5 /* tensor path: max |x| times the scale of the fp16 point planes; must stay
+                                  below 32768 (only a streamed load can exceed it, see kmc_accumulate_rows) */
 #define KMC_STAT_COUNT       8
 
 /* Version of this ABI (major*1000 + minor). */
@@ -92,6 +94,21 @@ int kmc_bind_workspace(kmc_ctx* ctx, void* dev_workspace, int64_t bytes);
  * hi/lo planes the tcgen05 kernel reads.
  */
 int kmc_bind_points(kmc_ctx* ctx, const float* dev_points, void* stream);
+
+/*
+ * Streamed loading (tensor path): overlap the first Lloyd iteration with the H2D copy of the points.
+ * kmc_bind_points_streamed binds the (still empty) device buffer; as soon as rows [r0, r1) have arrived
+ * kmc_accumulate_rows splits them into the fp16 planes, assigns them and ADDS their sums / counts / inertia
+ * to the partial buffer (zeroed by the piece that starts at row 0).  Pieces are consecutive, start at row 0 and
+ * end at multiples of 128 (the last one at n_rows); after the last piece the context is in the same state as
+ * after kmc_bind_points + kmc_accumulate, so kmc_update and further kmc_accumulate / kmc_iterate calls follow.
+ * The plane scale is fixed by the first piece: if KMC_STAT_X_SCALED_MAX reads >= 32768 afterwards (later
+ * rows more than 8x larger than every row of the first piece) rebind with kmc_bind_points and repeat the
+ * iteration.  KMC_E_UNSUPPORTED on the small-D and SIMT paths (bind normally there).  No counterpart in the
+ * reference, whose feed of `X` (:273) completes before the first `sess.run` of the loop (:277).
+ */
+int kmc_bind_points_streamed(kmc_ctx* ctx, const float* dev_points, void* stream);
+int kmc_accumulate_rows(kmc_ctx* ctx, int64_t r0, int64_t r1, void* stream);
 
 /*
  * Pinned, double-buffered host->device staging of rows [row0, row0+n_rows) of a host array

@@ -17,6 +17,7 @@ KMC_EMPTY_KEEP, KMC_EMPTY_NAN = 0x0, 0x1
 KMC_PATH_AUTO, KMC_PATH_SMALL, KMC_PATH_SIMT, KMC_PATH_TC = 0x00, 0x10, 0x20, 0x30
 KMC_DTYPE_F32, KMC_DTYPE_F64 = 0, 1
 KMC_STAT_INERTIA, KMC_STAT_SHIFT2, KMC_STAT_AMBIGUOUS, KMC_STAT_KERNEL_PATH, KMC_STAT_LAUNCHES = 0, 1, 2, 3, 4
+KMC_STAT_X_SCALED_MAX = 5
 KMC_STAT_COUNT = 8
 KMC_PARAM_TC_GAMMA = 1
 KMC_PARAM_PROFILE = 2
@@ -46,6 +47,8 @@ SIGNATURES = {
     "kmc_accumulate_add": (c_int, [c_void_p, c_void_p]),
     "kmc_update": (c_int, [c_void_p, c_void_p]),
     "kmc_iterate": (c_int, [c_void_p, c_int, c_double, POINTER(c_int), POINTER(c_double), POINTER(c_double), c_void_p]),
+    "kmc_bind_points_streamed": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "kmc_accumulate_rows": (c_int, [c_void_p, c_int64, c_int64, c_void_p]),
     "kmc_assign": (c_int, [c_void_p, c_void_p, c_void_p]),
     "kmc_labels_to_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "kmc_read_stats": (c_int, [c_void_p, POINTER(c_double), c_void_p]),

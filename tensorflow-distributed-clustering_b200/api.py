@@ -113,6 +113,46 @@ class LloydShard:
                                                   row0 + r, nr, self._stream()))
         self.bind_points(pts)
 
+    def stage_and_accumulate_from_host(self, host, row0: int, piece_rows=None) -> bool:
+        """H2D of rows [row0, row0 + n_rows) in pieces on a copy stream, each piece assigned and accumulated
+        (the first Lloyd iteration; centroids must be set) while the next piece is on its way.  Leaves the
+        shard as after stage_from_host() + accumulate().  Returns False -- having done nothing -- where streamed
+        loading does not apply (small-D / SIMT path); falls back to a plain rebind + accumulate() if the plane
+        scale fixed by the first piece turned out too small for later rows."""
+        torch = _torch()
+        if self.stats()["path"] != "tc" or self.n < (1 << 16):
+            return False
+        if isinstance(host, torch.Tensor):
+            arr_ptr, is64 = host.data_ptr(), host.dtype == torch.float64
+            if host.dtype not in (torch.float32, torch.float64) or not host.is_contiguous():
+                raise ValueError("host tensor must be contiguous float32/float64")
+        else:
+            if host.dtype not in (np.float32, np.float64) or not host.flags.c_contiguous:
+                raise ValueError("host array must be C-contiguous float32/float64")
+            arr_ptr, is64 = host.ctypes.data, host.dtype == np.float64
+        piece = int(piece_rows) if piece_rows else max(1 << 20, -(-self.n // 8))
+        piece = -(-piece // 128) * 128
+        with torch.cuda.device(self.device):
+            pts = torch.empty((self.n, self.D), dtype=torch.float32, device=self.device)
+            compute = torch.cuda.current_stream(self.device)
+            copy = torch.cuda.Stream(self.device)
+            copy.wait_stream(compute)
+            L.check(self.lib.kmc_bind_points_streamed(self._ctx, c_void_p(pts.data_ptr()), self._stream()))
+            self.points = pts
+            for r0 in range(0, self.n, piece):
+                r1 = min(self.n, r0 + piece)
+                L.check(self.lib.kmc_stage_points(self._ctx, c_void_p(pts.data_ptr() + r0 * self.D * 4), c_void_p(arr_ptr),
+                                                  L.KMC_DTYPE_F64 if is64 else L.KMC_DTYPE_F32, row0 + r0, r1 - r0,
+                                                  c_void_p(copy.cuda_stream)))
+                landed = torch.cuda.Event()
+                landed.record(copy)
+                compute.wait_event(landed)
+                L.check(self.lib.kmc_accumulate_rows(self._ctx, r0, r1, self._stream()))
+            if self.stats()["x_scaled_max"] >= 32768.0:      # later rows overflowed the planes' fp16 range
+                self.bind_points(pts)
+                self.accumulate()
+        return True
+
     def set_centroids(self, C):
         C = np.ascontiguousarray(np.asarray(C, dtype=np.float32))
         if C.shape != (self.K, self.D):
@@ -177,7 +217,7 @@ class LloydShard:
             L.check(self.lib.kmc_read_stats(self._ctx, buf, self._stream()))
         return {
             "inertia": buf[L.KMC_STAT_INERTIA], "shift2": buf[L.KMC_STAT_SHIFT2],
-            "ambiguous": int(buf[L.KMC_STAT_AMBIGUOUS]),
+            "ambiguous": int(buf[L.KMC_STAT_AMBIGUOUS]), "x_scaled_max": buf[L.KMC_STAT_X_SCALED_MAX],
             "path": L.PATH_NAMES.get(int(buf[L.KMC_STAT_KERNEL_PATH]), "?"),
             "launches": int(buf[L.KMC_STAT_LAUNCHES]),
         }
@@ -257,7 +297,7 @@ def allreduce_partials_single_process(shards):
     torch.cuda.nccl.all_reduce([s.partials for s in shards])
 
 
-def lloyd_loop(shards, n_max_iters: int, tol: float = 0.0, reduce_fn=None):
+def lloyd_loop(shards, n_max_iters: int, tol: float = 0.0, reduce_fn=None, first_accumulated: bool = False):
     """Iterate ``n_max_iters`` times (reference :277-280): accumulate on every shard, sum the
     partial buffers across shards, update on every shard (identical arithmetic on identical
     inputs keeps the replicated centroids bit-identical, so no broadcast is needed).
@@ -267,14 +307,16 @@ def lloyd_loop(shards, n_max_iters: int, tol: float = 0.0, reduce_fn=None):
     place -- across the list, and across processes when every rank runs this loop on its own
     shard (``reduce_fn = lambda s: torch.distributed.all_reduce(s[0].partials)``).
     ``tol > 0`` stops when the squared centre shift drops to ``tol`` (same decision on every
-    rank: the shift is computed from the reduced buffer).  Returns (iterations, inertia, shift2).
+    rank: the shift is computed from the reduced buffer).  ``first_accumulated``: the shards already hold
+    the partial sums of the first iteration (streamed loading).  Returns (iterations, inertia, shift2).
     """
     if reduce_fn is None:
         reduce_fn = allreduce_partials_single_process
     n_iter, inertia, shift2 = 0, float("nan"), float("nan")
-    for _ in range(int(n_max_iters)):
-        for s in shards:
-            s.accumulate()
+    for it in range(int(n_max_iters)):
+        if not (first_accumulated and it == 0):
+            for s in shards:
+                s.accumulate()
         reduce_fn(shards)
         for s in shards:
             s.update()
@@ -320,7 +362,7 @@ def _prefaulted_labels(n: int):
 
 def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_iters=20, *,
                          seed=None, batch_size=None, tol=0.0, empty="keep", path="auto",
-                         return_labels=True, out_of_core=None):
+                         return_labels=True, out_of_core=None, stream_first_iteration=True):
     """Data-parallel K-Means (Lloyd) on one or more B200s -- drop-in for the reference function.
 
     Accepts both reference call shapes: ``(data_batch, K, GPU_names, initial_centers,
@@ -331,7 +373,8 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     shard does not fit in HBM.  ``GPU_names`` is a list of device names as returned by the reference's
     ``get_available_gpus()`` (or an int = number of GPUs).  ``batch_size`` = rows per pinned H2D
     staging chunk; ``tol`` = optional early stop on the squared centre shift (0 = run all
-    ``n_max_iters`` like the reference).
+    ``n_max_iters`` like the reference).  ``stream_first_iteration``: on the tensor path with one GPU per
+    process, form the first iteration's sums piece by piece while the rows are still being copied to the GPU.
 
     Returns the reference's result dictionary (:284-292): ``end_center``, ``cluster_idx``,
     ``centroids`` (labels of the last GPU's shard), ``init_center``, ``setup_time``,
@@ -380,22 +423,33 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
 
     # ---- initialisation: H2D of every shard + centroids (:272-274) ----
     initialization_ts = time.time()
+    streamed = False
     for s, (r0, r1) in zip(shards, ranges):
+        s.set_centroids(init_center)
         if on_device:
             blk = data[r0:r1]
             if blk.device != s.device or blk.dtype != torch.float32 or not blk.is_contiguous():
                 blk = blk.to(device=s.device, dtype=torch.float32).contiguous()
             s.bind_points(blk)
+        elif len(shards) == 1 and n_max_iters >= 1 and stream_first_iteration:
+            # the sums of the first iteration are formed piece by piece while the rows are still arriving
+            streamed = s.stage_and_accumulate_from_host(data, r0, batch_size if batch_size and batch_size >= (1 << 20) else None)
+            if not streamed:
+                s.stage_from_host(data, r0, batch_size)
         else:
             s.stage_from_host(data, r0, batch_size)
-        s.set_centroids(init_center)
     for s in shards:
         torch.cuda.synchronize(s.device)
     initialization_time = float(time.time() - initialization_ts)
 
     # ---- the Lloyd loop (:277-280) ----
     aux_ts = time.time()
-    if len(shards) == 1:
+    if streamed:
+        n_iter, inertia, shift2 = lloyd_loop(shards, 1, tol, reduce_fn=lambda sh: None, first_accumulated=True)
+        if n_max_iters > 1 and not (tol > 0.0 and shift2 <= tol):
+            more, inertia, shift2 = shards[0].iterate(n_max_iters - 1, tol)
+            n_iter += more
+    elif len(shards) == 1:
         n_iter, inertia, shift2 = shards[0].iterate(n_max_iters, tol)
     else:
         n_iter, inertia, shift2 = lloyd_loop(shards, n_max_iters, tol)
@@ -503,7 +557,8 @@ def _fits_in_hbm(n_rows, D, K, device, empty, path) -> bool:
 
 
 def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *, device=None, batch_size=None,
-                              tol=0.0, empty="keep", path="auto", return_labels=True, group=None):
+                              tol=0.0, empty="keep", path="auto", return_labels=True, group=None,
+                              stream_first_iteration=True):
     """The same Lloyd loop with ONE PROCESS PER GPU (torchrun): every rank passes the rows the
     reference's array_split rule (:184) gives it (`shard_ranges(N, world)[rank]`) and the same
     initial centres; the per-GPU partial sums meet in one NCCL all-reduce per iteration
@@ -524,18 +579,22 @@ def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *,
     setup_time = float(time.time() - setup_ts)
 
     initialization_ts = time.time()
+    shard.set_centroids(init_center)
+    streamed = False
     if isinstance(rows, torch.Tensor) and rows.is_cuda:
         shard.bind_points(rows.to(device=device, dtype=torch.float32).contiguous())
     else:
-        shard.stage_from_host(rows, 0, batch_size)
-    shard.set_centroids(init_center)
+        if int(n_max_iters) >= 1 and stream_first_iteration:
+            streamed = shard.stage_and_accumulate_from_host(rows, 0, batch_size if batch_size and batch_size >= (1 << 20) else None)
+        if not streamed:
+            shard.stage_from_host(rows, 0, batch_size)
     torch.cuda.synchronize(device)
     initialization_time = float(time.time() - initialization_ts)
 
     aux_ts = time.time()
     distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
     reduce_fn = (lambda s: dist.all_reduce(s[0].partials, group=group)) if distributed else (lambda s: None)
-    n_iter, inertia, shift2 = lloyd_loop([shard], int(n_max_iters), tol, reduce_fn=reduce_fn)
+    n_iter, inertia, shift2 = lloyd_loop([shard], int(n_max_iters), tol, reduce_fn=reduce_fn, first_accumulated=streamed)
     torch.cuda.synchronize(device)
     computation_time = float(time.time() - aux_ts)
 

@@ -60,6 +60,9 @@ static int check_ready(kmc_ctx* c, bool need_centroids) {
     if (!c->ws) KMC_FAIL(KMC_E_STATE, "workspace not bound (kmc_bind_workspace)");
     if (!c->points && c->n > 0) KMC_FAIL(KMC_E_STATE, "points not bound (kmc_bind_points)");
     if (need_centroids && !c->have_centroids) KMC_FAIL(KMC_E_STATE, "centroids not set (kmc_set_centroids)");
+    if (c->streaming)
+        KMC_FAIL(KMC_E_STATE, "streamed load incomplete: %lld of %lld rows delivered (kmc_accumulate_rows)",
+                 (long long)c->stream_rows, (long long)c->n);
     return 0;
 }
 
@@ -309,11 +312,59 @@ int kmc_bind_points(kmc_ctx* c, const float* dev_points, void* stream) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     c->points = dev_points;
     c->planes_ready = false;
+    c->streaming = false;
     if (c->path == KMC_PATH_TC) {
         KMC_CUDA(cudaMemsetAsync(&c->stats()->x_absmax_bits, 0, sizeof(unsigned int), s));
         KMC_TRY(launch_absmax(c, dev_points, c->n * c->D, &c->stats()->x_absmax_bits, s));
         KMC_TRY(launch_split_points(c, s));
         KMC_TRY(tc_setup_tensor_maps(c));
+    }
+    return 0;
+}
+
+int kmc_bind_points_streamed(kmc_ctx* c, const float* dev_points, void* stream) {
+    if (!c) KMC_FAIL(KMC_E_INVALID, "null context");
+    if (!c->ws) KMC_FAIL(KMC_E_STATE, "bind the workspace before the points");
+    if (!dev_points && c->n > 0) KMC_FAIL(KMC_E_INVALID, "null points");
+    if (reinterpret_cast<uintptr_t>(dev_points) & 3) KMC_FAIL(KMC_E_INVALID, "points must be 4-byte aligned");
+    if (c->path != KMC_PATH_TC || c->n < kTcBlockM)
+        KMC_FAIL(KMC_E_UNSUPPORTED, "streamed loading exists for the tensor path only; use kmc_bind_points");
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    c->points = dev_points;
+    c->planes_ready = false;
+    c->streaming = true;
+    c->stream_rows = 0;
+    KMC_CUDA(cudaMemsetAsync(&c->stats()->x_absmax_bits, 0, sizeof(unsigned int), s));
+    KMC_TRY(tc_setup_tensor_maps(c));
+    return 0;
+}
+
+int kmc_accumulate_rows(kmc_ctx* c, int64_t r0, int64_t r1, void* stream) {
+    if (!c) KMC_FAIL(KMC_E_INVALID, "null context");
+    if (!c->streaming) KMC_FAIL(KMC_E_STATE, "kmc_accumulate_rows needs kmc_bind_points_streamed first");
+    if (!c->have_centroids) KMC_FAIL(KMC_E_STATE, "centroids not set (kmc_set_centroids)");
+    if (r0 != c->stream_rows || r1 <= r0 || r1 > c->n || (r1 < c->n && r1 % kTcBlockM))
+        KMC_FAIL(KMC_E_INVALID, "rows [%lld, %lld): pieces are consecutive from row %lld and end at multiples of %d",
+                 (long long)r0, (long long)r1, (long long)c->stream_rows, kTcBlockM);
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool first = r0 == 0;
+    if (first) KMC_CUDA(cudaMemsetAsync(c->partials(), 0, (size_t)kmc_partials_len(c) * 8, s));
+    // the first piece fixes the power-of-two scale of the fp16 planes (|X'| < 2^12 leaves 16x head-room in
+    // fp16 for larger values in later pieces; KMC_STAT_X_SCALED_MAX tells the caller whether that was enough)
+    KMC_TRY(launch_absmax(c, c->points + r0 * c->D, (r1 - r0) * c->D, &c->stats()->x_absmax_bits, s));
+    KMC_TRY(launch_split_points_range(c, r0, r1, !first, s));
+    KMC_TRY(ensure_planes(c, s));
+    tc_policy_poll(c);
+    KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
+    KMC_TRY(tc_pass(c, c->labels(), r0, r1, 0, s));
+    KMC_TRY(refine_worklist(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[0], s));
+    KMC_TRY(launch_sorted_accumulate(c, c->labels(), r0, r1, 0, s));
+    c->stream_rows = r1;
+    if (r1 == c->n) {
+        c->streaming = false;
+        KMC_TRY(tc_policy_post(c, s));
     }
     return 0;
 }
@@ -499,6 +550,7 @@ int kmc_read_stats(kmc_ctx* c, double* host_stats, void* stream) {
     host_stats[KMC_STAT_AMBIGUOUS] = (double)amb;
     host_stats[KMC_STAT_KERNEL_PATH] = (double)c->path;
     host_stats[KMC_STAT_LAUNCHES] = (double)c->launches;
+    host_stats[KMC_STAT_X_SCALED_MAX] = (double)__builtin_bit_cast(float, st.x_absmax_bits) * (double)st.sigma_x;
     return 0;
 }
 

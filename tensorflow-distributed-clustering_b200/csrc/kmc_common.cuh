@@ -99,6 +99,8 @@ struct kmc_ctx {
     const float* points = nullptr;
     bool have_centroids = false;
     bool planes_ready = false;
+    bool streaming = false;             // kmc_bind_points_streamed: rows arrive in pieces (kmc_accumulate_rows)
+    int64_t stream_rows = 0;            // rows delivered and accumulated so far
     // tensor maps (opaque 128-byte blobs, 64-byte aligned)
     alignas(64) CUtensorMap tmap_xhi;
     alignas(64) CUtensorMap tmap_xlo;
@@ -140,6 +142,7 @@ int launch_convert_f64(const double* src, float* dst, int64_t count, cudaStream_
 int launch_widen_labels(const int32_t* src, long long* dst, int64_t count, cudaStream_t s);
 int launch_absmax(kmc_ctx* c, const float* x, int64_t count, unsigned int* out_bits, cudaStream_t s);
 int launch_split_points(kmc_ctx* c, cudaStream_t s);
+int launch_split_points_range(kmc_ctx* c, int64_t r0, int64_t r1, bool keep_scale, cudaStream_t s);
 // assign_small.cu
 bool small_path_supported(int64_t K, int64_t D);
 int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s);

@@ -73,16 +73,19 @@ int launch_absmax(kmc_ctx* c, const float* x, int64_t count, unsigned int* out_b
 
 // One warp per row: X'_hi = fp16(x * sigma), X'_lo = fp16(x * sigma - X'_hi) (both at the same
 // scale), zero padding up to D_pad, and xnorm'[row] = |x * sigma| rounded up.
-__global__ void __launch_bounds__(256) split_points_kernel(const float* __restrict__ x, int64_t n, int D,
+// Rows [row0, n).  keep_scale != 0: use the scale already in stats->sigma_x (rows arriving in pieces must all
+// be split at the scale chosen for the first piece).
+__global__ void __launch_bounds__(256) split_points_kernel(const float* __restrict__ x, int64_t row0, int64_t n, int D,
                                                            int D_pad, __half* __restrict__ xhi,
                                                            __half* __restrict__ xlo,
-                                                           float* __restrict__ xnorm, DeviceStats* stats) {
-    const float sigma = scale_from_absmax(__uint_as_float(stats->x_absmax_bits));
-    if (blockIdx.x == 0 && threadIdx.x == 0) stats->sigma_x = sigma;
+                                                           float* __restrict__ xnorm, DeviceStats* stats,
+                                                           int keep_scale) {
+    const float sigma = keep_scale ? stats->sigma_x : scale_from_absmax(__uint_as_float(stats->x_absmax_bits));
+    if (!keep_scale && blockIdx.x == 0 && threadIdx.x == 0) stats->sigma_x = sigma;
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t row = warp; row < n; row += nwarps) {
+    for (int64_t row = row0 + warp; row < n; row += nwarps) {
         const float* xr = x + row * (int64_t)D;
         __half* hr = xhi + row * (int64_t)D_pad;
         __half* lr = xlo + row * (int64_t)D_pad;
@@ -105,14 +108,16 @@ __global__ void __launch_bounds__(256) split_points_kernel(const float* __restri
     }
 }
 
-int launch_split_points(kmc_ctx* c, cudaStream_t s) {
-    int64_t blocks = (c->n + 7) / 8;
+int launch_split_points(kmc_ctx* c, cudaStream_t s) { return launch_split_points_range(c, 0, c->n, false, s); }
+
+int launch_split_points_range(kmc_ctx* c, int64_t r0, int64_t r1, bool keep_scale, cudaStream_t s) {
+    int64_t blocks = (r1 - r0 + 7) / 8;
     const int64_t cap = (int64_t)c->sm_count * 8;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    split_points_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->points, c->n, (int)c->D, (int)c->D_pad,
+    split_points_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->points, r0, r1, (int)c->D, (int)c->D_pad,
                                                          c->at<__half>(c->off_xhi), c->at<__half>(c->off_xlo),
-                                                         c->at<float>(c->off_xnorm), c->stats());
+                                                         c->at<float>(c->off_xnorm), c->stats(), keep_scale ? 1 : 0);
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;

@@ -277,6 +277,75 @@ def test_labels_to_host_int32_int64_pageable_and_pinned(pkg, cuda_device):
     s.close()
 
 
+def test_streamed_first_iteration_equals_the_plain_path(pkg, cuda_device):
+    """kmc_bind_points_streamed + kmc_accumulate_rows: rows arriving in pieces give the sums of one plain
+    accumulate over all rows, and the shard continues like a normally bound one."""
+    n, d, k = 150_000, 64, 64
+    X, _ = pkg.datagen.blobs_numpy(n, d, 40, seed=9)
+    C0 = X[:k].copy()
+    plain = _shard(pkg, X, k, cuda_device, path="tc")
+    plain.set_centroids(C0)
+    plain.accumulate()
+    want = plain.partials.cpu().numpy().copy()
+    for host in (X, X.astype(np.float64)):
+        s = pkg.LloydShard(n, d, k, cuda_device, path="tc")
+        s.set_centroids(C0)
+        with pytest.raises(pkg._lib.KmcError):
+            s.accumulate()                                       # nothing bound yet
+        assert s.stage_and_accumulate_from_host(host, 0, piece_rows=20_000)      # 8 pieces, ragged tail
+        got = s.partials.cpu().numpy()
+        assert np.array_equal(got[k * d:k * d + k], want[k * d:k * d + k])        # counts
+        assert oracle.rel_err(got[:k * d], want[:k * d]) <= 1e-6      # fp32 lane sums over different row runs
+        assert abs(got[k * d + k] - want[k * d + k]) <= 1e-6 * want[k * d + k]     # inertia
+        s.update()
+        s.iterate(2)
+        plain2 = _shard(pkg, X, k, cuda_device, path="tc")
+        plain2.set_centroids(C0)
+        plain2.iterate(3)
+        assert oracle.rel_err(s.get_centroids(), plain2.get_centroids()) <= 1e-6
+        plain2.close()
+        s.close()
+    plain.close()
+    # small-D shards do not stream
+    s = pkg.LloydShard(100_000, 2, 8, cuda_device)
+    s.set_centroids(X[:8, :2].copy())
+    assert s.stage_and_accumulate_from_host(np.ascontiguousarray(X[:100_000, :2]), 0) is False
+    s.close()
+
+
+def test_streamed_load_falls_back_when_later_rows_outgrow_the_plane_scale(pkg, cuda_device):
+    n, d, k = 120_000, 64, 64
+    X, _ = pkg.datagen.blobs_numpy(n, d, 40, seed=10)
+    X[:30_000] *= 1e-3                       # the first piece fixes a scale 1000x too large for the rest
+    C0 = X[40_000:40_000 + k].copy()
+    s = pkg.LloydShard(n, d, k, cuda_device, path="tc")
+    s.set_centroids(C0)
+    assert s.stage_and_accumulate_from_host(X, 0, piece_rows=30_000)
+    assert s.stats()["x_scaled_max"] < 32768.0                   # rebound at the global scale
+    plain = _shard(pkg, X, k, cuda_device, path="tc")
+    plain.set_centroids(C0)
+    plain.accumulate()
+    got, want = s.partials.cpu().numpy(), plain.partials.cpu().numpy()
+    assert np.array_equal(got[k * d:k * d + k], want[k * d:k * d + k]) and oracle.rel_err(got[:k * d], want[:k * d]) <= 1e-6
+    s.close()
+    plain.close()
+
+
+def test_drop_in_streams_the_first_iteration_on_large_tensor_shards(pkg, cuda_device):
+    n, d, k = 100_000, 64, 64
+    X, _ = pkg.datagen.blobs_numpy(n, d, 40, seed=12)
+    C0 = X[:k].copy()
+    ref = oracle.run_lloyd(X, C0, 3)
+    for stream in (True, False):
+        res = pkg.distribuited_k_means(X, k, 1, C0, 3, stream_first_iteration=stream)
+        assert res["n_iter"] == 3
+        assert oracle.rel_err(res["end_center"], ref["end_center"]) <= RTOL
+        assert len(oracle.label_mismatches(res["cluster_idx"], ref["cluster_idx"], ref["final_d1"], ref["final_d2"])) == 0
+        assert abs(res["inertia"] - ref["history"][-1]["inertia"]) <= RTOL * ref["history"][-1]["inertia"]
+    one = pkg.distribuited_k_means(X, k, 1, C0, 1)
+    assert one["n_iter"] == 1 and abs(one["inertia"] - ref["history"][0]["inertia"]) <= RTOL * ref["history"][0]["inertia"]
+
+
 def test_drop_in_entry_point_matches_oracle(pkg, cuda_device):
     X, _ = pkg.datagen.blobs_numpy(20000, 2, 8, seed=123128)
     X64 = X.astype(np.float64)                       # the reference feeds float64 (make_classification)
