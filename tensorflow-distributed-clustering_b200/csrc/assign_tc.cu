@@ -53,7 +53,8 @@ struct TcParams {
     const float* cnorm;
     DeviceStats* stats;
     int32_t* labels;
-    int32_t* worklist;
+    int32_t* worklist;   // non-null: uncertified rows are recorded (as bits of amb_mask; compacted afterwards)
+    uint32_t* amb_mask;  // one word per 32 rows (word index = row / 32): bit i = row 32*w + i is uncertified
     float* scores;       // debug: [n, K] or nullptr
     float gamma;         // accumulate + split error of the 3-term score, relative to |X'||C'|
     float gamma1;        // accumulate error of the 1-term score
@@ -574,16 +575,22 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             // ... and the column groups of the row through shared memory
             if (NPASS == 1 && kGroups == 2) {
                 // only the two warps that share a TMEM lane quarter meet, on their own named barrier
+                // Barrier 2+q: "half 1's result is in mg" (half 1 arrives without waiting, half 0 waits);
+                // barrier 6+q: "mg has been read" (half 0 arrives, half 1 waits for it only before its NEXT
+                // write).  Neither half ever waits for the other's end-of-tile work.
                 float* mg = cn_s + 8 * 128 + q * 96;
-                if (half == 1) { mg[lane] = m1; mg[32 + lane] = m2; mg[64 + lane] = __int_as_float(a1); }
-                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
-                if (half == 0) {
+                if (half == 1) {
+                    if (it > 0) asm volatile("bar.sync %0, 64;" ::"r"(6 + q) : "memory");
+                    mg[lane] = m1; mg[32 + lane] = m2; mg[64 + lane] = __int_as_float(a1);
+                    asm volatile("bar.arrive %0, 64;" ::"r"(2 + q) : "memory");
+                } else {
+                    asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
                     const float o1 = mg[lane], o2 = mg[32 + lane];
                     const int oa = __float_as_int(mg[64 + lane]);
+                    if (it + 1 < n_my_tiles) asm volatile("bar.arrive %0, 64;" ::"r"(6 + q) : "memory");
                     if (o1 < m1) { m2 = fminf(m1, o2); m1 = o1; a1 = oa; }
                     else { m2 = fminf(m2, o1); }
                 }
-                asm volatile("bar.sync %0, 64;" ::"r"(2 + q) : "memory");
             }
             float* mg = cn_s;                 // 3 terms: the bias buffer is idle here
 #pragma unroll
@@ -610,15 +617,11 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     const float pack_err = ((SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));
                     amb = p.worklist && (m2 - m1) <= thr + pack_err;
                 }
-                // one atomic per warp reserves the worklist slots of all its uncertified rows
+                // uncertified rows: one 32-bit mask per warp and row tile, no atomic and no dependent store on
+                // this path (a returning atomic here costs ~800 cycles per row tile in warps that hold two of the
+                // eight TMEM-buffer releases); compact_worklist_kernel turns the masks into the worklist
                 const unsigned mask = __ballot_sync(0xffffffffu, amb);
-                if (mask) {
-                    const int leader = __ffs(mask) - 1;
-                    unsigned long long base = 0;
-                    if (lane == leader) base = atomicAdd(p.amb_counter, (unsigned long long)__popc(mask));
-                    base = __shfl_sync(0xffffffffu, base, leader);
-                    if (amb) p.worklist[base + __popc(mask & ((1u << lane) - 1u))] = (int32_t)row;
-                }
+                if (p.worklist && lane == 0 && (row - lane) < p.n) p.amb_mask[(row - lane) >> 5] = mask;
             }
             if (!(NPASS == 1 && kGroups == 2)) asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
         }
@@ -667,6 +670,55 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
                      kTcBlockN));
     KMC_TRY(make_map(fn, &c->tmap_bias, c->at<void>(c->off_cbias), (uint64_t)kTcChunkK, (uint64_t)c->K_pad, kTcBlockN));
     c->tmaps_ready = true;
+    return 0;
+}
+
+// Worklist of the rows [32*w0, 32*(w0+nw)) from the masks the tensor kernel wrote: a warp takes 32 mask words,
+// reserves the slots of all their set bits with one atomic and writes the row numbers in ascending order
+// (consecutive worklist entries are rows close together in memory: the refine kernels gather whole rows).
+__global__ void __launch_bounds__(256) compact_worklist_kernel(const uint32_t* __restrict__ mask, int64_t w0, int64_t nw,
+                                                               int32_t* __restrict__ worklist,
+                                                               unsigned long long* __restrict__ counter,
+                                                               const unsigned int* __restrict__ gate_flag) {
+    if (gate_flag && *gate_flag == 0u) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t base = warp * 32; base < nw; base += nwarps * 32) {
+        const int64_t w = base + lane;
+        uint32_t word = (w < nw) ? mask[w0 + w] : 0u;
+        const int cnt = __popc(word);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        if (total == 0) continue;
+        unsigned long long pos = 0;
+        if (lane == 0) pos = atomicAdd(counter, (unsigned long long)total);
+        pos = __shfl_sync(0xffffffffu, pos, 0) + (unsigned long long)(incl - cnt);
+        const int32_t row0 = (int32_t)((w0 + w) << 5);
+        while (word) {
+            const int b = __ffs(word) - 1;
+            word &= word - 1u;
+            worklist[pos++] = row0 + b;
+        }
+    }
+}
+
+int launch_compact_worklist(kmc_ctx* c, int32_t* worklist, unsigned long long* amb_counter, int64_t r0, int64_t r1,
+                            const unsigned int* gate_flag, cudaStream_t s) {
+    const int64_t w0 = r0 >> 5, nw = ((r1 + 31) >> 5) - w0;
+    if (nw <= 0) return 0;
+    int64_t blocks = (nw + 255) / 256;
+    const int64_t cap = (int64_t)c->sm_count * 8;
+    blocks = blocks > cap ? cap : blocks;
+    compact_worklist_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->at<uint32_t>(c->off_ambmask), w0, nw, worklist, amb_counter,
+                                                             gate_flag);
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
     return 0;
 }
 
@@ -726,6 +778,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.stats = c->stats();
     p.labels = labels_out;
     p.worklist = worklist;
+    p.amb_mask = c->at<uint32_t>(c->off_ambmask);
     p.scores = scores_out;
     p.gamma = (float)c->tc_gamma;
     p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);

@@ -44,6 +44,7 @@ static void layout_workspace(kmc_ctx* c) {
     }
     if (c->path == KMC_PATH_TC) {
         c->off_xnorm = take(c->n * 8);          // per row: |X'| and |X' - X'_hi|, both rounded up
+        c->off_ambmask = take((c->n / 32 + 2) * 4);   // one bit per row: not certified by the tensor kernel
         c->off_cnorm = take(c->K_pad * 4);
         c->off_cbias = take(c->K_pad * kTcChunkK * 2);   // S*|c_k|^2 as fp16 pieces: one extra MMA k-step adds it
         c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
@@ -90,10 +91,12 @@ static int refine_worklist(kmc_ctx* c, int32_t* labels, const int32_t* worklist,
 static int tc_pass(kmc_ctx* c, int32_t* labels, int64_t r0, int64_t r1, int ch, cudaStream_t s) {
     unsigned long long* cnt = &c->stats()->n_amb[ch];
     KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, c->tc_terms_now, nullptr, s));
+    KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, nullptr, s));
     if (c->tc_terms == 0 && c->tc_terms_now == 1) {
         unsigned int* flag = &c->stats()->tc3_flag[ch];
         KMC_TRY(launch_tc_gate(c, cnt, flag, r1 - r0, s));
         KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, 3, flag, s));
+        KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, flag, s));
     }
     return 0;
 }

@@ -94,7 +94,7 @@ struct kmc_ctx {
     int64_t need_bytes = 0;
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_perm = 0,
             off_sort = 0, sort_stride = 0, sort_cursor = 0, sort_offsets = 0, sort_segoff = 0,
-            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0,
+            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0, off_ambmask = 0,
             off_ccdist = -1, off_nbr = -1;
     const float* points = nullptr;
     bool have_centroids = false;
@@ -157,6 +157,9 @@ int tc_setup_tensor_maps(kmc_ctx* c);
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
                      float* scores_out, int64_t r0, int64_t r1, int terms, const unsigned int* gate_flag,
                      cudaStream_t s);
+// rows [r0, r1) (r0 a multiple of 32): masks of uncertified rows -> worklist, their number added to *amb_counter
+int launch_compact_worklist(kmc_ctx* c, int32_t* worklist, unsigned long long* amb_counter, int64_t r0, int64_t r1,
+                            const unsigned int* gate_flag, cudaStream_t s);
 int launch_tc_gate(kmc_ctx* c, unsigned long long* amb_counter, unsigned int* flag, int64_t rows, cudaStream_t s);
 // refine.cu
 int launch_ccdist(kmc_ctx* c, cudaStream_t s);
