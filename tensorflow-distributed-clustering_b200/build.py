@@ -53,7 +53,7 @@ def build(force: bool = False, verbose: bool = False, ptxas_info: bool = False) 
         o = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
-            cmd = [nvcc, *NVCC_FLAGS, "-c", s, "-o", o]
+            cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("NVCC_EXTRA", "").split(), "-c", s, "-o", o]   # NVCC_EXTRA: e.g. -DKMC_TRACE
             if ptxas_info:
                 cmd[1:1] = ["-Xptxas", "-v"]
             jobs.append(cmd)

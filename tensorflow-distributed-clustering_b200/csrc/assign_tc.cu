@@ -42,6 +42,20 @@ constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
 constexpr float kPackRel = 1.6e-5f;                 // > 2^-16: relative weight of the 7 packed index bits
 
+// Optional cycle trace of the barrier hand-offs (build with -DKMC_TRACE; tools/trace_run.py reads it): CTA 0
+// stamps clock64 -- and %globaltimer at slot 1, which gives the SM clock the kernel really runs at -- for tile
+// steps 400..655.  Slots: 0/1 warp 4 before its t_full wait (cycles / ns), 2 t_full seen, 3 t_empty arrive,
+// 4 / 5 start / end of the end-of-row-tile section, 6 MMA issuer got the TMEM buffer, 7 issuer committed t_full.
+#ifdef KMC_TRACE
+__device__ long long g_trace[256][8];
+__device__ __forceinline__ long long trace_ns() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define KMC_TRACE_AT(step, k) do { if (blockIdx.x == 0 && (step) >= 400u && (step) < 656u) g_trace[(step) - 400u][k] = clock64(); } while (0)
+#define KMC_TRACE_NS(step, k) do { if (blockIdx.x == 0 && (step) >= 400u && (step) < 656u) g_trace[(step) - 400u][k] = trace_ns(); } while (0)
+#else
+#define KMC_TRACE_AT(step, k) do {} while (0)
+#define KMC_TRACE_NS(step, k) do {} while (0)
+#endif
+
 struct TcParams {
     int64_t n;
     int K, K_pad;
@@ -382,6 +396,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                     const uint32_t buf = ac & 1u;
                     mbar_wait<40>(t_empty(buf), ((ac >> 1) & 1u) ^ 1u, p.stats, 0x400u + buf);
+                    KMC_TRACE_AT(ac, 6);
                     tc_fence_after_sync();
                     const uint32_t d_tmem = tmem_base + buf * kTcBlockN;
                     uint32_t accum = 0;
@@ -429,6 +444,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         ++sb;
                     }
                     umma_commit(t_full(buf));
+                    KMC_TRACE_AT(ac, 7);
                 }
                 umma_commit(a_empty(abuf));
             }
@@ -498,7 +514,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
                     cn = cw + half * kCols;
                 }
+                if (threadIdx.x == 128) { KMC_TRACE_AT(ac, 0); KMC_TRACE_NS(ac, 1); }
                 mbar_wait<0>(t_full(buf), (ac >> 1) & 1u, p.stats, 0x700u + buf);
+                if (threadIdx.x == 128) KMC_TRACE_AT(ac, 2);
                 tc_fence_after_sync();
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kTcBlockN + half * kCols;
                 const float e_in = te.m1, o_in = to.m1, b_in = tb.m1;
@@ -525,6 +543,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 }
                 tc_fence_before_sync();
                 __syncwarp();
+                if (threadIdx.x == 128) KMC_TRACE_AT(ac, 3);
                 if (lane == 0) mbar_arrive(t_empty(buf));
                 // a changed best value carries its column in the low bits
                 if (__float_as_uint(te.m1) != __float_as_uint(e_in)) a_e = kbase + (int)(__float_as_uint(te.m1) & 0x7Fu);
@@ -532,6 +551,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 if (__float_as_uint(tb.m1) != __float_as_uint(b_in))
                     a_blk = kbase + (int)(__float_as_uint(tb.m1) & (uint32_t)(kEpiBlocksPerHalf - 1)) * kEpiG;
             }
+            if (threadIdx.x == 128) KMC_TRACE_AT((uint32_t)(it + 1) * (uint32_t)p.n_ntiles - 1u, 4);
             float m1, m2;
             int a1;
             if constexpr (SCORES || kOldEpi) {
@@ -622,6 +642,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 // eight TMEM-buffer releases); compact_worklist_kernel turns the masks into the worklist
                 const unsigned mask = __ballot_sync(0xffffffffu, amb);
                 if (p.worklist && lane == 0 && (row - lane) < p.n) p.amb_mask[(row - lane) >> 5] = mask;
+                if (threadIdx.x == 128) KMC_TRACE_AT((uint32_t)(it + 1) * (uint32_t)p.n_ntiles - 1u, 5);
             }
             if (!(NPASS == 1 && kGroups == 2)) asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
         }
@@ -799,3 +820,9 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
 }
 
 }  // namespace kmc
+
+#ifdef KMC_TRACE
+extern "C" int kmc_debug_trace(long long* host_out) {      // 256 x 8 stamps of the last tensor-kernel launch
+    return (int)cudaMemcpyFromSymbol(host_out, kmc::g_trace, sizeof(long long) * 256 * 8);
+}
+#endif
