@@ -35,6 +35,7 @@ namespace kmc {
 
 constexpr uint32_t kTileBytesA = kTcBlockM * 128;   // 128 rows x 128 B  = 16 KB per (plane, chunk)
 constexpr uint32_t kStageBytesB = kTcBlockN * 128;  // 256 rows x 128 B  = 32 KB per stage
+constexpr uint32_t kBiasStageBytes = kTcBlockN * kBiasCols * 2;   // 256 rows x 32 B = 8 KB of a B slot
 constexpr uint32_t kTmemCols = 512;
 // kind::f16, fp16 x fp16 -> fp32, A and B K-major, M = 128, N = 256
 constexpr uint32_t kInstrDesc = (1u << 4) | ((uint32_t)(kTcBlockN >> 3) << 17) | ((uint32_t)(kTcBlockM >> 4) << 24);
@@ -89,9 +90,10 @@ template <int KC, int NPASS> struct TcCfg {
 #endif
     static constexpr int kStages = (NPASS == 1) ? KMC_TC_STAGES1 : ((KC == 1) ? 4 : 3);
     static constexpr uint32_t kBBytes = kStages * kStageBytesB;
-    // 1 term: a constant 128 x 64 fp16 tile holding kBiasConst in its first columns; multiplied with a stage
-    // of the bias plane it makes the MMA add S*|c_k|^2 to the accumulator (no FADD per score in the epilogue)
-    static constexpr uint32_t kAExtBytes = (NPASS == 1) ? kTileBytesA : 0;
+    // 1 term: a constant 128 x 16 fp16 tile (32-byte swizzled) holding kBiasConst in its first columns; multiplied
+    // with a stage of the bias plane it makes the MMA add S*|c_k|^2 to the accumulator (no FADD per score in the
+    // epilogue)
+    static constexpr uint32_t kAExtBytes = (NPASS == 1) ? kTcBlockM * 32 : 0;      // 128 rows x 32 B
     static constexpr uint32_t kOther = kBBytes + kAExtBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 256;
     // the points tile is double buffered whenever two copies fit next to the B ring (227 KB per CTA)
     static constexpr int kABufs = (2 * kPlanes * KC * kTileBytesA + kOther <= 232448u) ? 2 : 1;
@@ -321,13 +323,13 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         tmem_relinquish();
     }
     if (AUG) {
-        // constant A tile of the bias step, in the 128-byte-swizzled K-major layout TMA would produce:
-        // row r, 16-byte chunk c lives at r*128 + ((c ^ (r & 7)) << 4); only chunk 0 is non-zero
+        // constant A tile of the bias step (128 rows x 16 fp16), in the 32-byte-swizzled K-major layout TMA
+        // would produce: row r, 16-byte chunk c lives at r*32 + ((c ^ ((r >> 2) & 1)) << 4); only chunk 0 is non-zero
         uint4* ext = reinterpret_cast<uint4*>(smem + Cfg::kAExtOff);
-        for (int i = threadIdx.x; i < (int)(kTileBytesA / 16); i += blockDim.x) ext[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = threadIdx.x; i < kTcBlockM * 2; i += blockDim.x) ext[i] = make_uint4(0u, 0u, 0u, 0u);
         __syncthreads();
         if (threadIdx.x < kTcBlockM) {
-            __half* row = reinterpret_cast<__half*>(smem + Cfg::kAExtOff + threadIdx.x * 128 + ((threadIdx.x & 7) << 4));
+            __half* row = reinterpret_cast<__half*>(smem + Cfg::kAExtOff + threadIdx.x * 32 + (((threadIdx.x >> 2) & 1) << 4));
 #pragma unroll
             for (int i = 0; i < kBiasPieces; ++i) row[i] = __float2half_rn(kBiasConst[i]);
         }
@@ -359,10 +361,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             load_a(0);
             for (int it = 0; it < n_my_tiles; ++it) {
                 for (int nt = 0; nt < p.n_ntiles; ++nt) {
-                    if (aug) {      // stage of the bias plane: 256 centroids x one 64-column chunk
+                    if (aug) {      // stage of the bias plane: 256 centroids x 16 columns (8 KB of the slot)
                         const int slot = sb % Cfg::kStages;
                         mbar_wait<100>(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x280u + slot);
-                        mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
+                        mbar_arrive_expect_tx(b_full(slot), kBiasStageBytes);
                         tma_load_2d_hint(smem_base + Cfg::kABytes + slot * kStageBytesB, &tm_bias, 0, nt * kTcBlockN,
                                          b_full(slot), kEvictLast);
                         ++sb;
@@ -404,8 +406,8 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         const int slot = sb % Cfg::kStages;
                         mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x580u + slot);
                         tc_fence_after_sync();
-                        umma_f16(d_tmem, umma_desc_sw128(smem_base + Cfg::kAExtOff),
-                                 umma_desc_sw128(smem_base + Cfg::kABytes + slot * kStageBytesB), kInstrDesc, 0);
+                        umma_f16(d_tmem, umma_desc_sw32(smem_base + Cfg::kAExtOff),
+                                 umma_desc_sw32(smem_base + Cfg::kABytes + slot * kStageBytesB), kInstrDesc, 0);
                         accum = 1;
                         umma_commit(b_empty(slot));
                         ++sb;
@@ -666,13 +668,14 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-static int make_map(EncodeTiledFn fn, CUtensorMap* m, void* base, uint64_t cols, uint64_t rows, uint32_t box_rows) {
+static int make_map(EncodeTiledFn fn, CUtensorMap* m, void* base, uint64_t cols, uint64_t rows, uint32_t box_rows,
+                    uint32_t box_cols = kTcChunkK, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
     cuuint64_t dims[2] = {cols, rows};
     cuuint64_t strides[1] = {cols * 2};
-    cuuint32_t box[2] = {(cuuint32_t)kTcChunkK, box_rows};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) KMC_FAIL(KMC_E_DEVICE, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return 0;
@@ -689,7 +692,8 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
     KMC_TRY(make_map(fn, &c->tmap_xlo, c->at<void>(c->off_xlo), (uint64_t)c->D_pad, (uint64_t)c->n, kTcBlockM));
     KMC_TRY(make_map(fn, &c->tmap_c, c->at<void>(c->off_cplanes), (uint64_t)c->D_pad, (uint64_t)(2 * c->K_pad),
                      kTcBlockN));
-    KMC_TRY(make_map(fn, &c->tmap_bias, c->at<void>(c->off_cbias), (uint64_t)kTcChunkK, (uint64_t)c->K_pad, kTcBlockN));
+    KMC_TRY(make_map(fn, &c->tmap_bias, c->at<void>(c->off_cbias), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN, kBiasCols,
+                     CU_TENSOR_MAP_SWIZZLE_32B));
     c->tmaps_ready = true;
     return 0;
 }

@@ -46,7 +46,7 @@ static void layout_workspace(kmc_ctx* c) {
         c->off_xnorm = take(c->n * 8);          // per row: |X'| and |X' - X'_hi|, both rounded up
         c->off_ambmask = take((c->n / 32 + 2) * 4);   // one bit per row: not certified by the tensor kernel
         c->off_cnorm = take(c->K_pad * 4);
-        c->off_cbias = take(c->K_pad * kTcChunkK * 2);   // S*|c_k|^2 as fp16 pieces: one extra MMA k-step adds it
+        c->off_cbias = take(c->K_pad * kBiasCols * 2);   // S*|c_k|^2 as fp16 pieces: one extra MMA k-step adds it
         c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
         c->off_ccdist = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;   // pruning table of the refine pass
         c->off_nbr = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;      // ... sorted nearest-first per centroid

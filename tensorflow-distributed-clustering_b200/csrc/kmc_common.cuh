@@ -41,6 +41,7 @@ constexpr int kStatSlots = 16;
 // score bias S*|c_k|^2 = sum_i kBiasConst[i] * piece_i with fp16 pieces (|piece| <= 65504): range 8.6e9,
 // resolution ~2^-10 absolute
 constexpr int kBiasPieces = 6;
+constexpr int kBiasCols = 16;     // fp16 columns of a bias-plane row (one K=16 MMA step, 32-byte swizzled rows)
 __device__ __constant__ const float kBiasConst[kBiasPieces] = {32768.f, 32768.f, 32768.f, 32768.f, 16.f, 0.0078125f};
 constexpr float kBiasMax = 2147483648.f;   // the plane is used only while max_k S*|c_k|^2 < 2^31
 constexpr int kMaxChunks = 4;    // row chunks of one accumulate pass (assign of chunk c+1 overlaps accumulate of chunk c)

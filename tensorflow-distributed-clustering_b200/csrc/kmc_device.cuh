@@ -180,4 +180,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
     return d;
 }
 
+// K-major, 32-byte-swizzled operand (rows of 32 bytes = one K=16 fp16 step, 8-row atoms 256 bytes apart):
+// the bias plane and its constant partner tile.
+__device__ __forceinline__ uint64_t umma_desc_sw32(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;                    // LBO (unused for swizzled K-major)
+    d |= (uint64_t)(256 >> 4) << 32;           // SBO = 256 bytes between 8-row groups
+    d |= (uint64_t)1 << 46;                    // descriptor version (Blackwell)
+    d |= (uint64_t)6 << 61;                    // SWIZZLE_32B
+    return d;
+}
+
 }  // namespace kmc

@@ -124,8 +124,8 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
         // 64-column chunk; the tensor kernel multiplies it with a constant tile holding the a_i, so the MMA
         // itself adds S*|c_k|^2 to every score.  Dead rows saturate (8.6e9, above every real score).
         {
-            __half* br = cbias + (int64_t)k * kTcChunkK;
-            for (int j = lane; j < kTcChunkK; j += 32) br[j] = __float2half_rn(0.f);
+            __half* br = cbias + (int64_t)k * kBiasCols;
+            if (lane < kBiasCols) br[lane] = __float2half_rn(0.f);
             __syncwarp();
             if (lane == 0) {
                 double r = (double)cn;
