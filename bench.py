@@ -318,6 +318,20 @@ def main():
     roofline["peak_source"] = peaks["source"] + (" bf16 dense, sustained" if roofline["bound"] == "tensor" else " copy bandwidth")
     roofline["kernel"] = {"tc": "tc_assign_kernel", "small": "small_kernel", "simt": "simt_assign_kernel"}[stats["path"]]
     roofline["kernel_ms"] = phases["assign"]
+    if stats["path"] == "tc" and (N // world) >= (1 << 22) and not any(kv.startswith("5=") for kv in args.param):
+        # In the timed region the tensor kernel shares the SMs (and the board's power budget) with the refine and
+        # the accumulation of the previous row chunk, which run on a side stream.  Two more iterations after the
+        # timed region, one kernel after the other (KMC_PARAM_CHUNKS = 1), give the kernel's own duration.
+        shard.set_param(pkg._lib.KMC_PARAM_CHUNKS, 1)
+        shard.phase_ms()
+        for _ in range(2):
+            one_step()
+        torch.cuda.synchronize(dev)
+        alone = shard.phase_ms()
+        if alone["assign"] > 0:
+            roofline["kernel_alone_ms"] = alone["assign"]
+            roofline["frac_alone"] = flops / (alone["assign"] * 1e-3) / 1e12 / peaks["tflops"]
+            roofline["phase_alone_ms"] = {k: round(v, 4) for k, v in alone.items() if k != "calls"}
     roofline["phase_ms"] = {k: round(v, 4) for k, v in phases.items() if k != "calls"}
     # whole-iteration roofline of BASELINE.json: slower of 2NKD at peak and 4ND at HBM bandwidth
     roofline["step_frac"] = max(t_tensor, t_hbm) / (ms_per_step * 1e-3)

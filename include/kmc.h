@@ -201,6 +201,9 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
 #define KMC_PARAM_REFINE_KERNEL 4 /* exact refine of uncertified rows: 4 = warp per row (long candidate walks),
                                    8 = eight lanes per row (short walks), 0 (default) = both enqueued, the
                                    device picks from the walk lengths of the previous launch */
+#define KMC_PARAM_CHUNKS    5   /* tensor path: row chunks per kmc_accumulate (1..4).  With more than one chunk the
+                                   refine and the accumulation of chunk c run on a side stream while the tensor
+                                   kernel assigns chunk c+1; 1 = strictly one kernel after the other */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 
 /*

@@ -652,6 +652,11 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             if (value != 0.0 && value != 4.0 && value != 8.0) KMC_FAIL(KMC_E_INVALID, "refine kernel must be 0, 4 or 8");
             c->refine_kernel = (int)value;
             return 0;
+        case KMC_PARAM_CHUNKS:
+            if (value < 1.0 || value > (double)kMaxChunks || value != (double)(int)value)
+                KMC_FAIL(KMC_E_INVALID, "row chunks must be an integer in 1..%d", kMaxChunks);
+            c->n_chunks = (int)value;
+            return 0;
         case KMC_PARAM_PROFILE:
             c->profile = value != 0.0;
             c->prof_acc_n = c->prof_upd_n = 0;
