@@ -6,23 +6,25 @@
 //   S = sigma_x*sigma_c  (powers of two), so score' = S * (|c_k|^2 - 2 x_i.c_k) = S*(d - |x|^2).
 //
 // fp32 accuracy from fp16 tensor inputs: every operand is split at staging time into two fp16
-// planes at one scale (v = hi + lo, |lo| <= 2^-11 |hi|) and three MMAs accumulate
-// hi*hi + lo*hi + hi*lo into one TMEM accumulator (the dropped lo*lo term is 2^-22 relative).
-// This is the 3-term split BASELINE.json asks for, issued as kind::f16 instead of kind::tf32:
-// same ~2^-22 operand accuracy, half the tensor time per term, and the two fp16 planes occupy
-// exactly the 4 bytes/element of the original fp32 point (same HBM traffic as the roofline counts).
+// planes at one scale (v = hi + lo, |lo| <= 2^-11 |hi|).  Three MMAs (hi*hi + lo*hi + hi*lo, NPASS = 3)
+// accumulate the fp32-accurate score BASELINE.json asks for (kind::f16 instead of kind::tf32: same ~2^-22
+// operand accuracy, half the tensor time per term, and the two planes are exactly the 4 bytes/element of
+// the fp32 point).  The default (NPASS = 1) issues hi*hi only and bounds the dropped terms per row.
 //
-// The epilogue keeps, per row, the best and second-best score and the best index.  Rows whose two
-// best scores are closer than a rigorous bound on the score error (2*gamma*|X'_i|*max_k|C'_k|) are
-// appended to a worklist and re-decided by the exact fp32 difference-form kernel
-// (assign_simt.cu), so the final labels equal an exact fp32 argmin with lowest-index ties.
+// The epilogue finds, per row, the exact best and second-best score of the accumulator values (partition
+// epilogue below: 1.44 min/max/logic instructions per score).  Rows whose two best scores are closer than a
+// rigorous bound on the score error are flagged in a bit mask (one word per warp and row tile, no atomics
+// in this kernel); compact_worklist_kernel turns the masks into a worklist and the exact fp32
+// difference-form kernels (refine.cu; assign_simt.cu for K > 8192) re-decide those rows, so the final
+// labels equal an exact fp32 argmin with lowest-index ties whatever NPASS was.
 //
 // Warp roles (384 threads, one CTA per SM, persistent over 128-row tiles):
 //   warp 0  TMA producer      warp 1  MMA issuer (one thread)     warp 2  TMEM alloc/dealloc
-//   warps 4-11  epilogue: tcgen05.ld 32 lanes x 32 columns, running top-2 in registers (two warps
-//   per TMEM lane quarter, each scanning one 128-column half of the accumulator tile)
-// Pipelines: A tiles (points, resident for the whole K sweep, double buffered when they fit),
-// B stages (centroid plane chunks, 3-4 deep ring), two TMEM accumulators of 256 columns.
+//   warps 4-11  epilogue: tcgen05.ld 32 lanes x 32 columns (two warps per TMEM lane quarter, each scanning
+//   one 128-column half of the accumulator tile; they meet once per row tile on one-way named barriers)
+// Pipelines: A tiles (points, resident for the whole K sweep, double buffered when they fit), B stages
+// (256 centroids x 64 columns, 3-4 deep ring; with AUG one 8 KB bias-plane stage per tile adds S*|c_k|^2
+// through an extra K=16 MMA), two TMEM accumulators of 256 columns.
 //
 // Replaces reference scripts/distribuitedClustering.py:221-234 for shapes where K*D makes the
 // distance computation a dense contraction.
