@@ -451,6 +451,7 @@ int kmc_resize(kmc_ctx* c, int64_t n_rows) {
                  (long long)n_rows, (long long)c->n_cap);
     c->n = n_rows;
     c->points = nullptr;          // the next batch must be bound before use
+    c->streaming = false;
     c->tmaps_ready = false;
     return 0;
 }
