@@ -95,6 +95,40 @@ def test_run_experiments_averages_batch_centres(pkg):
     assert (out["setup_time"], out["initialization_time"], out["computation_time"], out["n_iter"]) == (2.0, 4.0, 6.0, 7)
 
 
+def test_lloyd_loop_can_start_from_an_already_accumulated_first_iteration(pkg):
+    """Streamed loading leaves the partial sums of iteration 1 in the shards: lloyd_loop(first_accumulated=True)
+    must skip exactly that accumulate and otherwise be the plain loop (same centres, counts of iterations, tol)."""
+    from test_distributed_gloo import OracleShard
+
+    X, _ = pkg.datagen.blobs_numpy(4000, 3, 6, seed=4)
+    C0 = X[:6].astype(np.float64)
+    ranges = pkg.shard_ranges(len(X), 2)
+
+    def reduce_on_cpu(shards):                       # the single-process default sums CUDA buffers with NCCL
+        total = sum(s.partials for s in shards)
+        for s in shards:
+            s.partials.copy_(total)
+
+    plain = [OracleShard(X[a:b], C0) for a, b in ranges]
+    n_plain, inertia_plain, shift_plain = pkg.lloyd_loop(plain, 5, reduce_fn=reduce_on_cpu)
+    pre = [OracleShard(X[a:b], C0) for a, b in ranges]
+    calls = []
+    for s in pre:
+        s.accumulate()
+        real = s.accumulate
+        s.accumulate = (lambda real=real: (calls.append(1), real())[1])
+    n_pre, inertia_pre, shift_pre = pkg.lloyd_loop(pre, 5, reduce_fn=reduce_on_cpu, first_accumulated=True)
+    assert n_pre == n_plain == 5 and len(calls) == 2 * 4
+    assert np.array_equal(pre[0].C, plain[0].C) and np.array_equal(pre[1].C, plain[1].C)
+    assert inertia_pre == inertia_plain and shift_pre == shift_plain
+    # tolerance stop right after the pre-accumulated iteration
+    one = [OracleShard(X[a:b], C0) for a, b in ranges]
+    for s in one:
+        s.accumulate()
+    n_one, _, shift_one = pkg.lloyd_loop(one, 50, tol=1e30, reduce_fn=reduce_on_cpu, first_accumulated=True)
+    assert n_one == 1 and shift_one <= 1e30
+
+
 def test_drop_in_script_exposes_reference_names():
     import importlib.util
 
