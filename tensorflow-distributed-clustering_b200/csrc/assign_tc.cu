@@ -639,7 +639,21 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     if (a1 >= p.K) a1 = 0;
                     p.labels[row] = a1;
                     const float pack_err = ((SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));
-                    amb = p.worklist && (m2 - m1) <= thr + pack_err;
+                    float thr_row = thr;
+                    if (NPASS == 1) {
+                        // Tighter bound on the dropped x_lo.(c_k - c_b): |c_k - c_b| <= |x - c_k| + |x - c_b|, and the
+                        // distances follow from the scores themselves (P = score + S|x|^2 = S*d, each known to
+                        // +-thr/2).  The right-hand side grows more slowly in the score of k than the gap does, so
+                        // holding for the second best it holds for every k.  The x.(c_lo,k - c_lo,b) part and the
+                        // accumulator rounding stay as they are.
+                        const float sx2 = xn * xn * (sigma_c / sigma_x);          // S*|x|^2, rounded up
+                        const float rho = 2.f * xlo * sqrtf(sigma_c / sigma_x);
+                        const float r1 = sqrtf(fmaxf(m1 + sx2 + 0.5f * thr, 0.f));
+                        const float r2 = sqrtf(fmaxf(m2 + sx2 + 0.5f * thr, 0.f));
+                        const float tight = rho * (r1 + r2) * 1.001f + 2.f * (xn * clomax + p.gamma1 * xn * cmax);
+                        if (r2 > rho) thr_row = fminf(thr, tight);                // (monotonicity needs r > rho / 2)
+                    }
+                    amb = p.worklist && !((m2 - m1) > thr_row + pack_err);        // NaNs count as uncertified
                 }
                 // uncertified rows: one 32-bit mask per warp and row tile, no atomic and no dependent store on
                 // this path (a returning atomic here costs ~800 cycles per row tile in warps that hold two of the
