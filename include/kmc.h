@@ -188,6 +188,13 @@ int kmc_assign(kmc_ctx* ctx, int32_t* dev_labels, void* stream);
 int kmc_labels_to_host(kmc_ctx* ctx, const int32_t* dev_labels, void* host_labels, int label_bytes,
                        int64_t n_labels, void* stream);
 
+/*
+ * dev_out[i, :] = centroids[dev_labels[i], :] (fp32 [n_rows, D] on the device; NaN rows for labels outside
+ * [0, K)): the recoloured points of the colour-quantisation use case, which the reference's notebook forms on
+ * the host as `center[label.flatten()]` (notebooks/Testing Images.ipynb:1233-1235).
+ */
+int kmc_gather_centroids(kmc_ctx* ctx, const int32_t* dev_labels, float* dev_out, void* stream);
+
 /* Synchronise `stream` and copy KMC_STAT_COUNT doubles (see KMC_STAT_*) to the host. */
 int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
 

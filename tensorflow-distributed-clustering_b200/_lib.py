@@ -51,6 +51,7 @@ SIGNATURES = {
     "kmc_bind_points_streamed": (c_int, [c_void_p, c_void_p, c_void_p]),
     "kmc_accumulate_rows": (c_int, [c_void_p, c_int64, c_int64, c_void_p]),
     "kmc_assign": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "kmc_gather_centroids": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "kmc_labels_to_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "kmc_read_stats": (c_int, [c_void_p, POINTER(c_double), c_void_p]),
     "kmc_set_param": (c_int, [c_void_p, c_int, c_double]),

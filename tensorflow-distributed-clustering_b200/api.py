@@ -201,6 +201,19 @@ class LloydShard:
             L.check(self.lib.kmc_assign(self._ctx, c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    def recolour(self, dev_labels=None, out=None):
+        """Every row replaced by its centroid (`center[label]`, the reference notebook's colour quantisation
+        output): float32 CUDA tensor [n_rows, D].  `dev_labels`: int32 labels from assign() (computed if None)."""
+        torch = _torch()
+        with torch.cuda.device(self.device):
+            if dev_labels is None:
+                dev_labels = self.assign()
+            if out is None:
+                out = torch.empty((self.n, self.D), dtype=torch.float32, device=self.device)
+            L.check(self.lib.kmc_gather_centroids(self._ctx, c_void_p(dev_labels.data_ptr()), c_void_p(out.data_ptr()),
+                                                  self._stream()))
+        return out
+
     def labels_to_host(self, dev_labels, out: np.ndarray) -> np.ndarray:
         """Copy int32 device labels (from assign()) into the host array `out` (int32 or int64, contiguous):
         widened on the device, staged through pinned buffers, no pinned allocation of the result."""

@@ -637,6 +637,13 @@ int kmc_labels_to_host(kmc_ctx* c, const int32_t* dev_labels, void* host_labels,
     return 0;
 }
 
+int kmc_gather_centroids(kmc_ctx* c, const int32_t* dev_labels, float* dev_out, void* stream) {
+    if (!c || (c->n > 0 && (!dev_labels || !dev_out))) KMC_FAIL(KMC_E_INVALID, "null argument");
+    if (!c->ws || !c->have_centroids) KMC_FAIL(KMC_E_STATE, "no centroids yet");
+    KMC_CUDA(cudaSetDevice(c->device));
+    return launch_gather_centroids(c, dev_labels, dev_out, static_cast<cudaStream_t>(stream));
+}
+
 int kmc_set_param(kmc_ctx* c, int param, double value) {
     if (!c) KMC_FAIL(KMC_E_INVALID, "null context");
     switch (param) {

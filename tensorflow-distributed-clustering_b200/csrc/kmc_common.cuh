@@ -140,6 +140,7 @@ namespace kmc {
 // ---- kernels (one .cu each) -------------------------------------------------------------------
 // stage.cu
 int launch_convert_f64(const double* src, float* dst, int64_t count, cudaStream_t s);
+int launch_gather_centroids(kmc_ctx* c, const int32_t* labels, float* out, cudaStream_t s);
 int launch_widen_labels(const int32_t* src, long long* dst, int64_t count, cudaStream_t s);
 int launch_absmax(kmc_ctx* c, const float* x, int64_t count, unsigned int* out_bits, cudaStream_t s);
 int launch_split_points(kmc_ctx* c, cudaStream_t s);

@@ -41,6 +41,31 @@ int launch_widen_labels(const int32_t* src, long long* dst, int64_t count, cudaS
     return 0;
 }
 
+// out[i, :] = centroids[labels[i], :] -- the "recoloured" points of the colour-quantisation use case
+__global__ void __launch_bounds__(256) gather_centroids_kernel(const float* __restrict__ cent, const int32_t* __restrict__ labels,
+                                                               int64_t n, int D, int K, float* __restrict__ out) {
+    const int64_t total = n * D;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const int64_t i = e / D;
+        const int j = (int)(e - i * D);
+        const int l = labels[i];
+        out[e] = ((unsigned)l < (unsigned)K) ? cent[(int64_t)l * D + j] : __int_as_float(0x7fc00000);
+    }
+}
+
+int launch_gather_centroids(kmc_ctx* c, const int32_t* labels, float* out, cudaStream_t s) {
+    const int64_t total = c->n * c->D;
+    if (total <= 0) return 0;
+    int64_t blocks = (total + 255) / 256;
+    const int64_t cap = (int64_t)c->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    gather_centroids_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), labels, c->n, (int)c->D, (int)c->K, out);
+    KMC_CUDA(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
 // max |x| over a flat fp32 array (NaNs ignored), folded into *out_bits with atomicMax on the
 // bit pattern (non-negative floats order like unsigned ints).
 __global__ void __launch_bounds__(256) absmax_kernel(const float* __restrict__ x, int64_t count,

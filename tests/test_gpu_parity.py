@@ -256,6 +256,18 @@ def test_refine_kernels_agree_with_the_oracle_on_long_and_short_walks(kernel, pk
     s.close()
 
 
+def test_recolour_is_centre_of_label(pkg, cuda_device):
+    X = pkg.datagen.image_numpy(120, 160, seed=7)                      # the colour-quantisation use case
+    s = _shard(pkg, X, 16, cuda_device)
+    s.set_centroids(X[:16])
+    s.iterate(3)
+    lab = s.assign()
+    got = s.recolour(lab).cpu().numpy()
+    assert np.array_equal(got, s.get_centroids()[lab.cpu().numpy()])
+    assert np.array_equal(s.recolour().cpu().numpy(), got)
+    s.close()
+
+
 def test_labels_to_host_int32_int64_pageable_and_pinned(pkg, cuda_device):
     """kmc_labels_to_host: several staging chunks (> 16 MB of labels), both widths, pageable and pinned targets."""
     import torch
