@@ -9,7 +9,12 @@ A "step" is one Lloyd iteration over the whole (sharded) batch: assignment + per
 accumulation on every rank, one NCCL all-reduce of the K*D+K+2 partial doubles (N > 1), centroid
 update.  Points are generated on the device and stay resident (the reference keeps them in
 `tf.Variable`s, scripts/distribuitedClustering.py:217); N total rows are split over the ranks by
-the reference's array_split rule (:184), so the total work is fixed ("strong" scaling).
+the reference's array_split rule (:184), so the total work is fixed ("strong" scaling).  The data set is
+defined by global row blocks, so every GPU count clusters the SAME rows from the same initial centres
+(`config.checks.centroid_checksum` / `inertia` agree across --gpus 1, 2, 4, 8).
+
+After the timed region the final iteration is re-checked at full size against a float64 mirror of the oracle
+on the GPU (`config.checks.parity`), see oracle/gpu_mirror.py.
 
 One JSON line is printed by rank 0; see DESIGN.md section "Measurement" for every key.
 """
@@ -112,30 +117,6 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------
 # CPU baseline / reference arm: the oracle port of the reference's CPU path, on the host cores
 # ----------------------------------------------------------------------------------------------
-def cpu_reference_step_factory(D, K, kind, sample_rows):
-    """One bounded Lloyd iteration of the oracle (float64 restatement of reference :221-263) on a
-    `sample_rows` sample of the same workload, using all host threads BLAS gives it."""
-    import oracle
-
-    pkg = importlib.import_module("tensorflow-distributed-clustering_b200")
-    if kind == "image":
-        side = int(np.sqrt(sample_rows / (16 / 9)))
-        X = pkg.datagen.image_numpy(side, side * 16 // 9, SEED)
-        C = pkg.datagen.kmeanspp_init(X, K, SEED).astype(np.float64)
-    else:
-        X, _ = pkg.datagen.blobs_numpy(sample_rows, D, K, SEED)
-        C = X[:K].astype(np.float64)
-    form = "gemm" if K * D > 4096 else "diff"
-    state = {"C": C}
-
-    def step():
-        it = oracle.lloyd_iteration(X, state["C"], n_shards=1, form=form)
-        state["C"] = it["centroids"]
-        return it["inertia"]
-
-    return step, X.shape[0], form
-
-
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -143,48 +124,148 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+def blas_threads():
+    """Threads the loaded BLAS / OpenMP pools will really use (threadpoolctl), as a dict per library."""
+    try:
+        from threadpoolctl import threadpool_info
+        return {f"{i.get('user_api')}:{i.get('internal_api')}": i.get("num_threads") for i in threadpool_info()}
+    except Exception as e:
+        return {"error": repr(e)}
+
+
+def cpu_sample(cfg_name, sample_rows):
+    pkg = importlib.import_module("tensorflow-distributed-clustering_b200")
+    N, D, K, kind = CONFIGS[cfg_name]
+    if kind == "image":
+        side = int(np.sqrt(sample_rows / (16 / 9)))
+        X = pkg.datagen.image_numpy(side, side * 16 // 9, SEED)
+        C = pkg.datagen.kmeanspp_init(X, K, SEED).astype(np.float64)
+    else:
+        X, _ = pkg.datagen.blobs_numpy(sample_rows, D, K, SEED)
+        C = X[:K].astype(np.float64)
+    return X, C
+
+
+def time_cpu_arms(cfg_name, steps, warmup):
+    """The CPU implementations of the same Lloyd iteration, each on a bounded sample of the workload with every
+    host thread the affinity mask allows (BLAS / OpenMP pools pinned to that count with threadpoolctl):
+      port     the float64 NumPy restatement of reference :221-263 (oracle/), GEMM form where K*D > 4096
+      sklearn  sklearn.cluster.KMeans(init=C0, n_init=1, algorithm='lloyd', tol=0): the OpenMP multi-core
+               implementation of the same math (the reference's authors compared with a CPU library too,
+               notebooks/Testing Images.ipynb:347)
+      literal  (config c1 only) the reference-shaped [n, K, D] float64 broadcast of :221-230
+    Returns {name: {"value", "rows", "seconds_per_iteration", ...}}."""
+    import oracle
+    from threadpoolctl import threadpool_limits
+
+    N, D, K, kind = CONFIGS[cfg_name]
+    cores = host_cores()
+    out = {}
+    with threadpool_limits(limits=cores):
+        # --- port
+        rows = int(min(N, max(4096, 8e10 / (2.0 * K * D))))
+        X, C = cpu_sample(cfg_name, rows)
+        form = "gemm" if K * D > 4096 else "diff"
+        state = {"C": C}
+
+        def step():
+            it = oracle.lloyd_iteration(X, state["C"], n_shards=1, form=form)
+            state["C"] = it["centroids"]
+
+        for _ in range(max(1, warmup)):
+            step()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step()
+        dt = (time.perf_counter() - t0) / steps
+        out["port"] = {"value": X.shape[0] / dt, "rows": int(X.shape[0]), "seconds_per_iteration": dt,
+                       "what": f"float64 {form}-form NumPy restatement (oracle/)"}
+        # --- sklearn
+        try:
+            from sklearn.cluster import KMeans
+            rows_s = int(min(N, max(4096, 4e11 / (2.0 * K * D))))
+            Xs, Cs = cpu_sample(cfg_name, rows_s)
+            iters = max(2, steps)
+            km = KMeans(n_clusters=K, init=Cs.astype(np.float32), n_init=1, algorithm="lloyd", tol=0.0, max_iter=iters)
+            t0 = time.perf_counter()
+            km.fit(Xs)
+            dts = (time.perf_counter() - t0) / max(1, km.n_iter_)
+            out["sklearn"] = {"value": Xs.shape[0] / dts, "rows": int(Xs.shape[0]), "seconds_per_iteration": dts,
+                              "what": f"sklearn KMeans lloyd float32, {km.n_iter_} iterations incl. its set-up"}
+        except Exception as e:                       # report, never hide
+            out["sklearn"] = {"error": repr(e)}
+        # --- literal reference-shaped run (C1 only: [n, K, D] float64 fits)
+        if cfg_name == "c1":
+            Xl, Cl = cpu_sample(cfg_name, min(N, 250_000))
+            t0 = time.perf_counter()
+            oracle.literal_iteration(Xl, Cl, n_shards=1)
+            dtl = time.perf_counter() - t0
+            out["literal"] = {"value": Xl.shape[0] / dtl, "rows": int(Xl.shape[0]), "seconds_per_iteration": dtl,
+                              "what": "reference-shaped [n,K,D] float64 broadcast (:221-230), one iteration"}
+    return out
+
+
+def cpu_baseline_record(cfg_name, arms):
+    N, D, K, kind = CONFIGS[cfg_name]
+    best = max((k for k in arms if "value" in arms[k] and k != "literal"), key=lambda k: arms[k]["value"])
+    a = arms[best]
+    return {
+        "value": a["value"], "unit": UNIT, "cores": host_cores(), "kind": "port",
+        "sample": f"{a['rows']} rows of the {cfg_name} workload (D={D}, K={K}); fastest CPU arm = {best}: {a['what']}",
+        "blas_threads": blas_threads(),
+        "arms": {k: ({"value": v["value"], "rows": v["rows"], "what": v["what"]} if "value" in v else v) for k, v in arms.items()},
+    }
+
+
 def run_reference_arm(args, cfg_name):
+    """`--impl reference`: TensorFlow is not installable here, so the reference's CPU path is timed as its CPU
+    restatements (see time_cpu_arms) with all host threads; `value` is the fastest of them."""
     N, D, K, kind = CONFIGS[cfg_name]
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    per_step_flops = 8e10                      # ~ a few seconds of host BLAS per step
-    sample = int(min(N, max(4096, per_step_flops / (2.0 * K * D))))
-    step, rows, form = cpu_reference_step_factory(D, K, kind, sample)
-    for _ in range(args.warmup):
-        step()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    dt = time.perf_counter() - t0
-    value = rows * args.steps / dt
-    cores = host_cores()
-    sample_desc = f"{rows} rows of the {cfg_name} workload (D={D}, K={K}), float64 {form}-form oracle, {args.steps} iterations"
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the BLAS / OpenMP pools of this process would be
+    # created with one thread.  Run the measurement in a child with that variable removed.
+    if os.environ.get("OMP_NUM_THREADS") and not os.environ.get("KMC_BENCH_CHILD"):
+        import subprocess
+        env = {k: v for k, v in os.environ.items() if k not in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS")}
+        env["KMC_BENCH_CHILD"] = "1"
+        for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "TORCHELASTIC_RUN_ID"):
+            env.pop(k, None)
+        r = subprocess.run([sys.executable, os.path.abspath(__file__)] + sys.argv[1:], env=env, capture_output=True, text=True)
+        sys.stdout.write(r.stdout)
+        sys.stderr.write(r.stderr)
+        return
+    arms = time_cpu_arms(cfg_name, max(1, args.steps), args.warmup)
+    rec = cpu_baseline_record(cfg_name, arms)
+    value = rec["value"]
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * N / value,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64/f32 (see cpu_baseline.arms)",
         "data": "synthetic",
         "config": {"workload": workload_name(cfg_name), "N": N, "D": D, "K": K,
-                   "note": "TensorFlow is not installable here; the reference's CPU path is timed as its float64 NumPy restatement (oracle/)"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_desc},
+                   "note": "TensorFlow is not installable here; the reference's CPU path is timed as CPU implementations of "
+                           "the same Lloyd iteration on a bounded sample; ms_per_step is that rate scaled to N rows"},
+        "cpu_baseline": rec,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
 
 
-def ncu_traffic_bytes(path, n_local, D, K):
-    """dram__bytes_read + dram__bytes_write of the dominant kernel per launch, from the committed ncu
-    capture (profiles/r1_traffic.json), scaled to the rows this rank's launch covers; None if the
-    capture is of another shape."""
+def ncu_traffic_bytes(kernel, n_local, D, K):
+    """dram__bytes_read + dram__bytes_write of the dominant kernel per launch, from this round's committed
+    `ncu --set full` capture (profiles/r2_traffic.json; a profile cannot be taken inside a timed run), scaled to
+    the rows this rank's launch covers.  (bytes, source) -- (None, why) if no capture of this kernel and shape
+    is committed."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-            t = json.load(f)["tc_assign_kernel"]
-        if path == "tc" and t["D"] == D and t["K"] == K:
-            return t["dram_bytes"] * (n_local / t["rows"])
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
+            t = json.load(f)[kernel]
+        if t["D"] == D and t["K"] == K:
+            return t["dram_bytes"] * (n_local / t["rows"]), t.get("source", "profiles/r2_traffic.json")
+        return None, "profiles/r2_traffic.json holds another shape"
     except Exception:
-        pass
-    return None
+        return None, "no capture committed for this kernel"
 
 
 def workload_name(cfg_name):
@@ -204,8 +285,13 @@ def main():
     ap.add_argument("--rows", type=int, default=0, help="override total rows (debugging only; marks the line invalid)")
     ap.add_argument("--path", default="auto", choices=["auto", "small", "simt", "tc"])
     ap.add_argument("--param", action="append", default=[], help="tuning: ID=VALUE passed to kmc_set_param")
+    ap.add_argument("--data", default="blobs", choices=["blobs", "blobs4", "uniform"],
+                    help="blobs: K blobs, sigma 1 (BASELINE.json); blobs4: K/4 blobs, so ~4 centroids share a blob and few "
+                         "rows are certified by one MMA term; uniform: no cluster structure (speed envelope, not the headline)")
+    ap.add_argument("--sigma", type=float, default=1.0, help="blob standard deviation (1.0 = BASELINE.json)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -237,13 +323,15 @@ def main():
     r0, r1 = pkg.shard_ranges(N, world)[rank]
     n_local = r1 - r0
 
-    # ---- synthetic data, generated on the device, resident for the whole run ----
+    # ---- synthetic data, generated on the device, resident for the whole run; rows [r0, r1) of ONE data set ----
     if kind == "image":
         X = pkg.datagen.image_torch(2160, 3840, SEED, dev)[r0:r1].contiguous()
         C0 = pkg.datagen.kmeanspp_init(X[:: max(1, n_local // 65536)].cpu().numpy(), K, SEED) if rank == 0 else None
     else:
-        X, _ = pkg.datagen.blobs_torch(n_local, D, K, SEED, dev, stream=rank)   # same blobs on every rank
-        C0 = X[:K].cpu().numpy() if rank == 0 else None
+        k_true = max(2, K // 4) if args.data == "blobs4" else K
+        X, _ = pkg.datagen.blobs_torch(n_local, D, k_true, SEED, dev, sigma=args.sigma, row0=r0,
+                                       kind="uniform" if args.data == "uniform" else "blobs")
+        C0 = X[:K].cpu().numpy() if rank == 0 else None          # global rows 0..K-1 (reference convention, :325)
     c0_t = torch.from_numpy(C0).to(dev) if rank == 0 else torch.empty((K, D), dtype=torch.float32, device=dev)
     if world > 1:
         dist.broadcast(c0_t, 0)
@@ -296,10 +384,20 @@ def main():
     ms_per_step = ms_total / max(args.steps, 1)
     value = N * args.steps / (ms_total * 1e-3)
 
-    # ---- size-independent checks at the full size (cheap): counts sum to N, labels idempotent ----
-    part = shard.partials.clone()
+    # ---- checks at the full size: counts, and the SAME result whatever the number of GPUs ----
+    part = shard.partials.clone()                      # all-reduced: global sums / counts / inertia of the last step
     counts_sum = float(part[K * D:K * D + K].sum().item())
-    checks = {"counts_sum_equals_N": bool(counts_sum == N)}
+    cent = shard.centroids_dev.double()
+    weights = torch.arange(1, K * D + 1, dtype=torch.float64, device=dev).view(K, D) / float(K * D)
+    checks = {"counts_sum_equals_N": bool(counts_sum == N),
+              "inertia": float(part[K * D + K].item()),
+              "centroid_checksum": float(cent.nan_to_num().sum().item()),
+              "centroid_checksum_weighted": float((cent.nan_to_num() * weights).sum().item()),
+              "changed_rows_last_step": stats["changed_rows"], "full_pass_last_step": stats["full_pass"]}
+
+    # ---- parity of one more full iteration at the full size against the float64 mirror of the oracle (GPU) ----
+    if not args.no_parity:
+        checks["parity"] = parity_check(shard, X, K, D, dev, world)
 
     # ---- roofline of the dominant kernel (the assignment kernel) ----
     peaks = measured_peaks()
@@ -314,24 +412,11 @@ def main():
         roofline = {"bound": "hbm", "achieved": bytes_alg / t_assign / 1e9 if t_assign > 0 else None,
                     "peak": peaks["hbm_gbs"], "unit": "GB/s"}
     roofline["frac"] = (roofline["achieved"] / roofline["peak"]) if roofline["achieved"] else None
-    roofline["traffic"] = ncu_traffic_bytes(stats["path"], n_local, D, K)
-    roofline["peak_source"] = peaks["source"] + (" bf16 dense, sustained" if roofline["bound"] == "tensor" else " copy bandwidth")
     roofline["kernel"] = {"tc": "tc_assign_kernel", "small": "small_kernel", "simt": "simt_assign_kernel"}[stats["path"]]
+    roofline["traffic"], roofline["traffic_source"] = ncu_traffic_bytes(roofline["kernel"], n_local, D, K)
+    roofline["peak_source"] = peaks["source"] + (" bf16 dense, sustained (kernel timed inside a long step)"
+                                                 if roofline["bound"] == "tensor" else " copy bandwidth")
     roofline["kernel_ms"] = phases["assign"]
-    if stats["path"] == "tc" and (N // world) >= (1 << 22) and not any(kv.startswith("5=") for kv in args.param):
-        # In the timed region the tensor kernel shares the SMs (and the board's power budget) with the refine and
-        # the accumulation of the previous row chunk, which run on a side stream.  Two more iterations after the
-        # timed region, one kernel after the other (KMC_PARAM_CHUNKS = 1), give the kernel's own duration.
-        shard.set_param(pkg._lib.KMC_PARAM_CHUNKS, 1)
-        shard.phase_ms()
-        for _ in range(2):
-            one_step()
-        torch.cuda.synchronize(dev)
-        alone = shard.phase_ms()
-        if alone["assign"] > 0:
-            roofline["kernel_alone_ms"] = alone["assign"]
-            roofline["frac_alone"] = flops / (alone["assign"] * 1e-3) / 1e12 / peaks["tflops"]
-            roofline["phase_alone_ms"] = {k: round(v, 4) for k, v in alone.items() if k != "calls"}
     roofline["phase_ms"] = {k: round(v, 4) for k, v in phases.items() if k != "calls"}
     # whole-iteration roofline of BASELINE.json: slower of 2NKD at peak and 4ND at HBM bandwidth
     roofline["step_frac"] = max(t_tensor, t_hbm) / (ms_per_step * 1e-3)
@@ -347,10 +432,16 @@ def main():
                    "refined_rows_last_step": stats["ambiguous"], "checks": checks,
                    "iterations_timed": f"Lloyd iterations {args.warmup + 1}..{args.warmup + args.steps} of one run from C0 = X[0:K] "
                                        "(the e2e leg times the whole run from iteration 1)",
+                   "accumulation": "incremental: running fp64 sums updated with the rows whose label changed; a device-side "
+                                   "gate takes the full pass when more than a quarter of the rows moved (every N*K distance is "
+                                   "evaluated either way)" if stats["path"] != "small" else "fused into the assignment kernel",
                    "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; device-side fallback to the 3-term split for chunks where >60% of the rows need the refine)"
                    if stats["path"] == "tc" else None},
         "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
     }
+    if args.data != "blobs" or args.sigma != 1.0:
+        result["config"]["data_variant"] = {"data": args.data, "sigma": args.sigma,
+                                            "note": "speed-envelope run on harder data, not the BASELINE.json workload"}
     if args.rows:
         result["config"]["INVALID"] = "--rows override: not the BASELINE.json configuration"
 
@@ -358,31 +449,61 @@ def main():
     if not args.no_e2e:
         host, note = pinned_host_copy(X, n_local, D, K, dev)
         shard.close()
-        del shard, X, part
+        del shard, X, part, cent, weights
         torch.cuda.empty_cache()
         result["e2e"] = run_e2e(pkg, host, note, C0, D, K, args.steps, dev, world, N)
+        if world == 1:
+            result["e2e_pageable_f64"] = run_e2e_pageable_f64(pkg, host, C0, D, K, args.steps, dev)
         del host
     else:
         result["e2e"] = None
 
-    # ---- CPU baseline: the oracle port on the host cores, bounded sample (rank 0, N = 1 only) ----
+    # ---- CPU baseline: CPU implementations of the same iteration on the host cores, bounded sample (rank 0, N = 1) ----
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sample = int(min(N, max(4096, 8e10 / (2.0 * K * D))))
-        step, rows, form = cpu_reference_step_factory(D, K, kind, sample)
-        step()
-        t0 = time.perf_counter()
-        iters = 3
-        for _ in range(iters):
-            step()
-        dt = time.perf_counter() - t0
-        result["cpu_baseline"] = {
-            "value": rows * iters / dt, "unit": UNIT, "cores": host_cores(), "kind": "port",
-            "sample": f"{rows} rows of the same workload (D={D}, K={K}), float64 {form}-form oracle, {iters} iterations",
-        }
+        result["cpu_baseline"] = cpu_baseline_record(args.config, time_cpu_arms(args.config, 3, 1))
     if rank == 0:
         print(json.dumps(result))
     if world > 1:
         dist.destroy_process_group()
+
+
+def parity_check(shard, X, K, D, dev, world):
+    """One more Lloyd iteration at the FULL size, checked against the float64 mirror of the oracle
+    (oracle/gpu_mirror.py, the checker -- plain torch float64 on the same GPU): every row's label outside
+    near-ties (<= 1e-5 relative), counts, per-cluster sums, inertia of this rank's shard; with several ranks the
+    figures are the worst over ranks.  Reference :221-248 on the same rows and centroids."""
+    import torch
+    import torch.distributed as dist
+    from oracle import gpu_mirror
+
+    C = shard.centroids_dev.clone()
+    shard.accumulate()                                   # local sums / counts / inertia (not all-reduced)
+    torch.cuda.synchronize(dev)
+    part = shard.partials.clone()
+    labels = shard.last_labels()
+    stats = shard.stats()
+    chunk = max(1 << 14, min(1 << 18, (1 << 28) // max(K, 1)))       # ~2 GB of float64 distances per chunk
+    ref = gpu_mirror.lloyd_pass_f64(X, C, chunk_rows=chunk)
+    out = gpu_mirror.compare_pass(ref, labels, part[:K * D].view(K, D), part[K * D:K * D + K],
+                                  float(part[K * D + K].item()))
+    out["pass_was_incremental"] = not stats["full_pass"]
+    del ref
+    if world > 1:
+        keys = [k for k in out if isinstance(out[k], (int, float)) and not isinstance(out[k], bool)]
+        t = torch.tensor([float(out[k]) for k in keys], dtype=torch.float64, device=dev)
+        tsum = t.clone()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        for i, k in enumerate(keys):
+            summed = k in ("rows_checked", "label_mismatches_outside_near_ties", "label_differences_inside_near_ties",
+                           "near_tie_rows", "counts_abs_diff")
+            out[k] = (int(tsum[i].item()) if k != "counts_abs_diff" else float(tsum[i].item())) if summed else float(t[i].item())
+        # the shard keeps going: this pass must not leave different centroids on different ranks
+        dist.all_reduce(shard.partials)
+    shard.update()
+    out["ok"] = bool(out["label_mismatches_outside_near_ties"] == 0 and out["sums_rel_err"] <= 1e-4
+                     and out["inertia_rel_err"] <= 1e-4 and out["counts_abs_diff"] <= 2 * out["near_tie_rows"])
+    return out
 
 
 def pinned_host_copy(X_dev, N, D, K, dev):
@@ -440,6 +561,29 @@ def run_e2e(pkg, host, note, C0, D, K, steps, dev, world, n_total):
     if note:
         out["note"] = note
     return out
+
+
+def run_e2e_pageable_f64(pkg, host_f32, C0, D, K, steps, dev):
+    """The drop-in's real input (reference :303, notebooks/Testing Images.ipynb:329): an ordinary PAGEABLE float64
+    NumPy array handed to `distribuited_k_means`.  The array is a float64 copy of a bounded number of rows of the
+    same workload (a float64 copy of all 100M rows of config 4 would need 102 GB of host memory); the timed
+    region is the whole call: host threads copy into pinned chunks, H2D, fp64 -> fp32 on the device, plane split,
+    `steps` iterations, centroids and int64 labels back."""
+    import psutil
+    import torch
+
+    avail = psutil.virtual_memory().available
+    rows = int(min(host_f32.shape[0], 16 << 20, max(K, (avail - (8 << 30)) // (3 * D * 8))))
+    X64 = host_f32[:rows].numpy().astype(np.float64)          # pageable
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    res = pkg.distribuited_k_means(X64, K, [f"/device:GPU:{dev.index}"], C0.astype(np.float64), steps)
+    dt = time.perf_counter() - t0
+    return {"value": rows * res["n_iter"] / dt, "unit": UNIT, "rows": rows, "iterations": res["n_iter"], "seconds": dt,
+            "h2d_bytes_per_step": int(rows * D * 8 / max(steps, 1)),
+            "d2h_bytes_per_step": int((K * D * 4 + rows * 8) / max(steps, 1)),
+            "initialization_time": res["initialization_time"], "computation_time": res["computation_time"],
+            "input": "pageable float64 NumPy array (the reference's callers' dtype)"}
 
 
 if __name__ == "__main__":

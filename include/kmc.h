@@ -60,6 +60,10 @@ typedef struct kmc_ctx kmc_ctx;
 #define KMC_STAT_LAUNCHES    4  /* kernels launched by this ctx since creation */
 #define KMC_STAT_X_SCALED_MAX 5 /* tensor path: max |x| times the scale of the fp16 point planes; must stay
                                   below 32768 (only a streamed load can exceed it, see kmc_accumulate_rows) */
+#define KMC_STAT_CHANGED     6  /* rows whose label changed in the last kmc_accumulate (all rows for a full pass
+                                  decided by the host: first pass, after a rebind) */
+#define KMC_STAT_FULL_PASS   7  /* 1: the last kmc_accumulate summed every row; 0: it updated the running sums
+                                  with the changed rows only (KMC_PARAM_INCREMENTAL) */
 #define KMC_STAT_COUNT       8
 
 /* Version of this ABI (major*1000 + minor). */
@@ -135,8 +139,17 @@ float* kmc_centroids_ptr(kmc_ctx* ctx);
  * Replaces the distance / argmin sub-graph (:221-234), the K per-cluster gather+mean ops
  * (:237-242), the CPU bincount (:244-246) and the mean*count reconstruction (:248).
  * The N x K distance matrix is never formed.  Result: the partial buffer
- *   double[K*D] sums (row-major) | double[K] counts | double[1] inertia | double[1] reserved
+ *   double[K*D] sums (row-major) | double[K] counts | double[1] inertia | double[1] sum_i |x_i|^2
  * at kmc_partials_ptr(); it is overwritten by every call.
+ *
+ * Incremental accumulation (SIMT and tensor paths, KMC_PARAM_INCREMENTAL, on by default): the context keeps the
+ * labels of its previous pass and running fp64 sums / counts.  From the second call on, only the rows whose
+ * label changed are summed (added under the new label, subtracted under the old one, every value in fp64, so
+ * the running sums equal a fresh pass to ~1e-15), and the inertia follows from the sums as
+ * sum|x|^2 - 2 sum_k c_k.S_k + sum_k n_k|c_k|^2.  The decision is taken on the device: when more than a quarter
+ * of the rows changed, the same call sums every row as the first one does.  All N x K distances are evaluated
+ * in either case; results are those of the full pass.  Rebinding points or workspace, kmc_resize and
+ * kmc_accumulate_add reset the running state.
  */
 int kmc_accumulate(kmc_ctx* ctx, void* stream);
 double* kmc_partials_ptr(kmc_ctx* ctx);
@@ -178,6 +191,15 @@ int kmc_iterate(kmc_ctx* ctx, int max_iters, double tol, int* n_iter_out,
 int kmc_assign(kmc_ctx* ctx, int32_t* dev_labels, void* stream);
 
 /*
+ * Labels of the last kmc_accumulate pass (int32 [n_rows] into dev_labels): argmin against the centroids that
+ * pass used, i.e. BEFORE the kmc_update that followed it.  This is what the reference fetches as
+ * `best_centroids` in the same sess.run as the update (:279) and returns under the key `centroids` (:286).
+ * SIMT / tensor paths: a device copy of the labels the pass kept; small-D path (which keeps none): one
+ * label-only pass against the saved pre-update centroids.
+ */
+int kmc_last_labels(kmc_ctx* ctx, int32_t* dev_labels, void* stream);
+
+/*
  * Deliver `n_labels` int32 device labels (as written by kmc_assign) to HOST memory as int32
  * (label_bytes = 4) or int64 (label_bytes = 8: the dtype of the reference's `np.argmin(...)` result,
  * :282; widened on the device).  `host_labels` may be pageable -- chunks are staged through the
@@ -209,8 +231,10 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
                                    8 = eight lanes per row (short walks), 0 (default) = both enqueued, the
                                    device picks from the walk lengths of the previous launch */
 #define KMC_PARAM_CHUNKS    5   /* tensor path: row chunks per kmc_accumulate (1..4).  With more than one chunk the
-                                   refine and the accumulation of chunk c run on a side stream while the tensor
-                                   kernel assigns chunk c+1; 1 = strictly one kernel after the other */
+                                   exact refine of chunk c runs on a side stream while the tensor kernel assigns
+                                   chunk c+1; 1 (default) = strictly one kernel after the other */
+#define KMC_PARAM_INCREMENTAL 6 /* 1 (default): kmc_accumulate updates running sums with the changed rows only where
+                                   it can (see kmc_accumulate); 0: every pass sums every row */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 
 /*
@@ -261,7 +285,8 @@ int kmc_kmeanspp(int device, const float* dev_points, int64_t n_rows, int64_t D,
  *
  *   dev_points    fp32 [n_rows, D] row-major          dev_labels  int32 [n_rows], values in [0, K)
  *   dev_centroids fp32 [K, D] (for the inertia)       dev_partials double [K*D + K + 2], same layout
- *                                                      as kmc_partials_ptr(); overwritten
+ *                                                      as kmc_partials_ptr() (sums | counts |
+ *                                                      inertia | sum |x|^2); overwritten
  *
  * The first call on a device looks up the device address of that array (no allocation, but a
  * runtime call), so make the first call on each device outside any stream capture.  All calls on

@@ -13,6 +13,10 @@ reference op for op (each function cites file:line) and is cross-checked against
 independent implementation of the same math, ``sklearn.cluster.KMeans(algorithm='lloyd')``
 (``tests/golden/make_golden.py``), but it could not be checked against outputs of the
 reference itself.
+
+``gpu_mirror.py`` is the float64 restatement of the same arithmetic in torch on the GPU (SURVEY.md
+section 8c, "Oracle at full scale"), validated against ``kmeans_oracle`` at small N by the GPU tests; it is
+imported explicitly (``from oracle import gpu_mirror``) so that importing ``oracle`` needs no torch.
 """
 from . import kmeanspp_oracle  # noqa: F401  (restatement of the device k-means++, csrc/kmeanspp.cu)
 from .kmeans_oracle import (  # noqa: F401

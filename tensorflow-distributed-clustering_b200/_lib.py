@@ -18,12 +18,14 @@ KMC_PATH_AUTO, KMC_PATH_SMALL, KMC_PATH_SIMT, KMC_PATH_TC = 0x00, 0x10, 0x20, 0x
 KMC_DTYPE_F32, KMC_DTYPE_F64 = 0, 1
 KMC_STAT_INERTIA, KMC_STAT_SHIFT2, KMC_STAT_AMBIGUOUS, KMC_STAT_KERNEL_PATH, KMC_STAT_LAUNCHES = 0, 1, 2, 3, 4
 KMC_STAT_X_SCALED_MAX = 5
+KMC_STAT_CHANGED, KMC_STAT_FULL_PASS = 6, 7
 KMC_STAT_COUNT = 8
 KMC_PARAM_TC_GAMMA = 1
 KMC_PARAM_PROFILE = 2
 KMC_PARAM_TC_TERMS = 3
 KMC_PARAM_REFINE_KERNEL = 4
 KMC_PARAM_CHUNKS = 5
+KMC_PARAM_INCREMENTAL = 6
 KMC_PHASE_COUNT = 5
 PATH_NAMES = {KMC_PATH_SMALL: "small", KMC_PATH_SIMT: "simt", KMC_PATH_TC: "tc"}
 PATH_FLAGS = {"auto": KMC_PATH_AUTO, "small": KMC_PATH_SMALL, "simt": KMC_PATH_SIMT, "tc": KMC_PATH_TC}
@@ -51,6 +53,7 @@ SIGNATURES = {
     "kmc_bind_points_streamed": (c_int, [c_void_p, c_void_p, c_void_p]),
     "kmc_accumulate_rows": (c_int, [c_void_p, c_int64, c_int64, c_void_p]),
     "kmc_assign": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "kmc_last_labels": (c_int, [c_void_p, c_void_p, c_void_p]),
     "kmc_gather_centroids": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "kmc_labels_to_host": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
     "kmc_read_stats": (c_int, [c_void_p, POINTER(c_double), c_void_p]),

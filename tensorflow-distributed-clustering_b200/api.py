@@ -16,7 +16,6 @@ from ctypes import byref, c_double, c_int, c_void_p
 import numpy as np
 
 from . import _lib as L
-from .datagen import kmeanspp_init
 from .sharding import parse_gpu_names, shard_ranges
 
 
@@ -201,6 +200,17 @@ class LloydShard:
             L.check(self.lib.kmc_assign(self._ctx, c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    def last_labels(self, out=None):
+        """int32 CUDA tensor [n_rows]: the labels of the last accumulate() pass, i.e. the argmin against the
+        centroids BEFORE the update that followed it -- what the reference fetches as `best_centroids` in the
+        same sess.run as the update (:279) and returns as `centroids` (:286)."""
+        torch = _torch()
+        with torch.cuda.device(self.device):
+            if out is None:
+                out = torch.empty(self.n, dtype=torch.int32, device=self.device)
+            L.check(self.lib.kmc_last_labels(self._ctx, c_void_p(out.data_ptr()), self._stream()))
+        return out
+
     def recolour(self, dev_labels=None, out=None):
         """Every row replaced by its centroid (`center[label]`, the reference notebook's colour quantisation
         output): float32 CUDA tensor [n_rows, D].  `dev_labels`: int32 labels from assign() (computed if None)."""
@@ -233,6 +243,7 @@ class LloydShard:
             "ambiguous": int(buf[L.KMC_STAT_AMBIGUOUS]), "x_scaled_max": buf[L.KMC_STAT_X_SCALED_MAX],
             "path": L.PATH_NAMES.get(int(buf[L.KMC_STAT_KERNEL_PATH]), "?"),
             "launches": int(buf[L.KMC_STAT_LAUNCHES]),
+            "changed_rows": int(buf[L.KMC_STAT_CHANGED]), "full_pass": bool(buf[L.KMC_STAT_FULL_PASS]),
         }
 
     def set_param(self, param: int, value: float):
@@ -390,7 +401,7 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     process, form the first iteration's sums piece by piece while the rows are still being copied to the GPU.
 
     Returns the reference's result dictionary (:284-292): ``end_center``, ``cluster_idx``,
-    ``centroids`` (labels of the last GPU's shard), ``init_center``, ``setup_time``,
+    ``centroids`` (labels of the last GPU's shard in the final iteration, before its update), ``init_center``, ``setup_time``,
     ``initialization_time``, ``computation_time``, ``n_iter`` -- plus ``inertia``, ``center_shift``,
     ``converged``.
     """
@@ -480,7 +491,11 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
         toucher.join()
         for s, p, (r0, r1) in zip(shards, parts, ranges):
             s.labels_to_host(p, cluster_idx[r0:r1])
-        last_labels = cluster_idx[ranges[-1][0]:ranges[-1][1]]
+        if n_iter >= 1:
+            # `centroids` (:279, :286): the last GPU's labels of the final iteration, against the centroids
+            # BEFORE its update -- not a slice of cluster_idx, which is computed after it (:282)
+            last = shards[-1]
+            last_labels = last.labels_to_host(last.last_labels(), np.empty(last.n, dtype=np.int64))
     for s in shards:
         s.close()
 
@@ -496,6 +511,9 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
         "inertia": inertia,
         "center_shift": float(np.sqrt(shift2)) if shift2 == shift2 else float("nan"),
         "converged": bool(tol > 0.0 and shift2 <= tol),
+        # True: iteration 1 ran underneath the H2D copy and is part of initialization_time, not of
+        # computation_time (pass stream_first_iteration=False for the reference's timer split, :272-280)
+        "first_iteration_streamed": bool(streamed),
     }
 
 
@@ -612,17 +630,20 @@ def distribuited_k_means_spmd(local_rows, K, initial_centers, n_max_iters=20, *,
     computation_time = float(time.time() - aux_ts)
 
     end_center = shard.get_centroids()
+    last_labels = None
     if return_labels:
         dev_labels = shard.assign()
         toucher.join()
         shard.labels_to_host(dev_labels, labels)
+        if n_iter >= 1:
+            last_labels = shard.labels_to_host(shard.last_labels(), np.empty(n_local, dtype=np.int64))
     shard.close()
     return {
-        "end_center": end_center, "cluster_idx": labels, "centroids": labels, "init_center": init_center,
+        "end_center": end_center, "cluster_idx": labels, "centroids": last_labels, "init_center": init_center,
         "setup_time": setup_time, "initialization_time": initialization_time,
         "computation_time": computation_time, "n_iter": n_iter, "inertia": inertia,
         "center_shift": float(np.sqrt(shift2)) if shift2 == shift2 else float("nan"),
-        "converged": bool(tol > 0.0 and shift2 <= tol),
+        "converged": bool(tol > 0.0 and shift2 <= tol), "first_iteration_streamed": bool(streamed),
     }
 
 
@@ -653,6 +674,7 @@ def _k_means_out_of_core(data, K, dev_ids, ranges, init_center, n_max_iters, bat
         cluster_idx = np.empty(N, dtype=np.int64)
         for s in shards:
             s.assign_to_host(cluster_idx)
+        # (the pre-update labels of the final iteration are not kept per batch: the slice of cluster_idx stands in)
         last_labels = cluster_idx[ranges[-1][0]:ranges[-1][1]]
     for s in shards:
         s.close()

@@ -1,10 +1,21 @@
 // Per-cluster sums, counts and inertia for large K*D, where per-CTA private accumulators do not
 // fit on chip and a scatter-add of N*D values through atomics would be ~10x slower than HBM.
-// Instead the labels are counting-sorted into a row permutation (rows of one cluster become a
+//
+// FULL pass: the labels are counting-sorted into a row permutation (rows of one cluster become a
 // contiguous run) and each run is summed with plain coalesced row loads:
-//     histogram -> exclusive scan -> scatter (perm) -> segmented row sum (+ exact inertia)
-// One extra streaming pass over the fp32 points, no atomics on the data path; fp32 partial sums
-// over <= 128 rows per lane, fp64 from the CTA level upward.
+//     histogram -> exclusive scan -> scatter (perm) -> segmented row sum (+ exact inertia, + sum |x|^2)
+// One extra streaming pass over the fp32 points, no atomics on the data path.
+//
+// INCREMENTAL pass (kmc_accumulate from the second call on): Lloyd iterations move fewer and fewer rows, so
+// the context keeps the labels of the previous pass and running fp64 sums / counts, finds the rows whose
+// label changed (diff_labels_kernel), and runs the same sort + segmented sum over THOSE rows only -- once
+// keyed by the new label (+x) and once by the old one (-x).  Every value is added in fp64 (an fp32 point is
+// exact in fp64, and the running sums carry 2^-53 relative rounding per addition), so the running sums equal
+// a fresh full pass to ~1e-15 whatever the number of iterations.  The inertia of such a pass follows from the
+// sums:  sum_i |x_i - c_l(i)|^2 = sum_i |x_i|^2 - 2 sum_k c_k.S_k + sum_k n_k |c_k|^2  (fp64; sum |x|^2 is a
+// constant of the data, formed by the first full pass).  Whether a pass is incremental is decided ON THE
+// DEVICE (more changed rows than the list holds -> full pass): both variants are enqueued, gated on a flag,
+// and the stream never waits for the host.
 //
 // Replaces reference scripts/distribuitedClustering.py:237-242 (K x equal/where/gather/reduce_mean),
 // :244-246 (D2H of the labels + CPU bincount) and :248 (mean*count = sum).  Sums are formed
@@ -17,17 +28,38 @@ namespace kmc {
 constexpr int kSegRows = 1024;        // rows of one cluster summed by one CTA
 constexpr int kScatterChunk = 16384;  // rows per CTA in the scatter pass
 
+// Which rows a sort kernel walks: rows r of a contiguous range (rows == nullptr: entry i is row i of `labels`,
+// recorded as row_base + i) or the entries of a row list whose length is known on the device only.
+struct RowSet {
+    const int32_t* labels;                 // contiguous: labels of the range; list: labels of ALL rows (indexed by row)
+    const int32_t* rows;                   // list of global row numbers, or nullptr
+    int64_t n;                             // entries (contiguous) / capacity of the list
+    const unsigned long long* n_dev;       // list: number of valid entries (clamped to n)
+    int64_t row_base;
+    const unsigned int* gate;              // nullptr, or: run only if *gate == gate_want
+    unsigned int gate_want;
+    __device__ __forceinline__ bool off() const { return gate && *gate != gate_want; }
+    __device__ __forceinline__ int64_t count() const {
+        if (!n_dev) return n;
+        const unsigned long long v = *n_dev;
+        return v < (unsigned long long)n ? (int64_t)v : n;
+    }
+    __device__ __forceinline__ int label(int64_t i) const { return rows ? labels[rows[i]] : labels[i]; }
+    __device__ __forceinline__ int32_t row(int64_t i) const { return rows ? rows[i] : (int32_t)(row_base + i); }
+};
+
 // ---- histogram --------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) hist_kernel(const int32_t* __restrict__ labels, int64_t n, int K,
-                                                   unsigned int* __restrict__ hist, int use_smem) {
+__global__ void __launch_bounds__(256) hist_kernel(const RowSet rs, int K, unsigned int* __restrict__ hist, int use_smem) {
     extern __shared__ unsigned int lh[];
+    if (rs.off()) return;
+    const int64_t n = rs.count();
     if (use_smem) {
         for (int i = threadIdx.x; i < K; i += blockDim.x) lh[i] = 0;
         __syncthreads();
     }
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const int l = labels[i];
+        const int l = rs.label(i);
         if ((unsigned)l < (unsigned)K) {
             if (use_smem) atomicAdd(&lh[l], 1u); else atomicAdd(&hist[l], 1u);
         }
@@ -45,9 +77,11 @@ __global__ void __launch_bounds__(256) hist_kernel(const int32_t* __restrict__ l
 __global__ void __launch_bounds__(1024) scan_kernel(const unsigned int* __restrict__ hist, int K,
                                                     unsigned int* __restrict__ offsets,
                                                     unsigned int* __restrict__ segoff,
-                                                    double* __restrict__ counts_out) {
+                                                    double* __restrict__ counts_out, double sign,
+                                                    const unsigned int* __restrict__ gate, unsigned int gate_want) {
     __shared__ unsigned int tot_rows[1024];
     __shared__ unsigned int tot_segs[1024];
+    if (gate && *gate != gate_want) return;
     const int t = threadIdx.x;
     const int per = (K + 1023) / 1024;
     const int b = t * per, e = min(K, b + per);
@@ -74,7 +108,7 @@ __global__ void __launch_bounds__(1024) scan_kernel(const unsigned int* __restri
         const unsigned int h = hist[i];
         offsets[i] = ro;
         segoff[i] = so;
-        counts_out[i] += (double)h;          // chunks of one pass add up (the buffer starts at zero)
+        if (h) counts_out[i] += sign * (double)h;   // chunks of one pass add up (the buffer starts at zero)
         ro += h;
         so += (h + kSegRows - 1) / kSegRows;
     }
@@ -82,26 +116,28 @@ __global__ void __launch_bounds__(1024) scan_kernel(const unsigned int* __restri
 }
 
 // ---- scatter: perm[offsets[l] + rank] = row ----------------------------------------------------
-__global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict__ labels, int64_t n, int K,
-                                                      const unsigned int* __restrict__ offsets,
+__global__ void __launch_bounds__(256) scatter_kernel(const RowSet rs, int K, const unsigned int* __restrict__ offsets,
                                                       unsigned int* __restrict__ cursor,
-                                                      int32_t* __restrict__ perm, int use_smem, int64_t row_base) {
+                                                      int32_t* __restrict__ perm, int use_smem) {
     extern __shared__ unsigned int sm[];
+    if (rs.off()) return;
+    const int64_t n = rs.count();
     unsigned int* lcnt = sm;        // [K] local counts, then local cursors
     unsigned int* lbase = sm + K;   // [K] global position of this CTA's first row of each cluster
     const int64_t r0 = (int64_t)blockIdx.x * kScatterChunk;
     const int64_t r1 = min(n, r0 + (int64_t)kScatterChunk);
+    if (r0 >= r1) return;
     if (!use_smem) {
         for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
-            const int l = labels[i];
-            if ((unsigned)l < (unsigned)K) perm[offsets[l] + atomicAdd(&cursor[l], 1u)] = (int32_t)(row_base + i);
+            const int l = rs.label(i);
+            if ((unsigned)l < (unsigned)K) perm[offsets[l] + atomicAdd(&cursor[l], 1u)] = rs.row(i);
         }
         return;
     }
     for (int i = threadIdx.x; i < K; i += blockDim.x) lcnt[i] = 0;
     __syncthreads();
     for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
-        const int l = labels[i];
+        const int l = rs.label(i);
         if ((unsigned)l < (unsigned)K) atomicAdd(&lcnt[l], 1u);
     }
     __syncthreads();
@@ -112,8 +148,8 @@ __global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict_
     }
     __syncthreads();
     for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
-        const int l = labels[i];
-        if ((unsigned)l < (unsigned)K) perm[lbase[l] + atomicAdd(&lcnt[l], 1u)] = (int32_t)(row_base + i);
+        const int l = rs.label(i);
+        if ((unsigned)l < (unsigned)K) perm[lbase[l] + atomicAdd(&lcnt[l], 1u)] = rs.row(i);
     }
 }
 
@@ -133,21 +169,25 @@ template <> struct RowVec<1> {
 
 // One CTA sums one run of <= kSegRows rows of one cluster.  Each warp owns a contiguous slice of the
 // run: it reads 32 permutation entries with one coalesced load, then keeps 8/P rows (512 B each at
-// D=128) in flight per lane group before folding them into fp32 accumulators -- the gather is
-// latency-bound, so bytes in flight per SM are what sets the bandwidth.
+// D=128) in flight per lane group before folding them into its accumulators -- the gather is
+// latency-bound, so bytes in flight per SM are what sets the bandwidth.  The accumulators are fp64 (the
+// running sums of the incremental pass must equal a fresh pass; the DADDs hide under the loads).
+// FULL: also the exact difference-form inertia against `cent` and sum |x|^2; otherwise `sign` * sums only.
 #ifdef KMC_SEGSUM_MAXNREG
 #define KMC_SEGSUM_ATTR __maxnreg__(KMC_SEGSUM_MAXNREG)
 #else
 #define KMC_SEGSUM_ATTR __launch_bounds__(256)
 #endif
-template <int VEC, int P>
+template <int VEC, int P, bool FULL>
 __global__ void KMC_SEGSUM_ATTR
 segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict__ cent,
               const int32_t* __restrict__ perm, const unsigned int* __restrict__ offsets,
-              const unsigned int* __restrict__ segoff, double* __restrict__ partials, int lpr_log2) {
+              const unsigned int* __restrict__ segoff, double* __restrict__ sums, double* __restrict__ scalars,
+              int lpr_log2, double sign, const unsigned int* __restrict__ gate, unsigned int gate_want) {
     constexpr int U = 8 / P;                   // row groups in flight
-    __shared__ float red[8][32 * VEC * P];
-    __shared__ double red_in[8];
+    __shared__ double red[8][32 * VEC * P];
+    __shared__ double red_in[8][2];
+    if (gate && *gate != gate_want) return;
     const unsigned int seg_total = segoff[K];
     const unsigned int b = blockIdx.x;
     if (b >= seg_total) return;
@@ -169,7 +209,8 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
     const int cl = lane & (LPR - 1), sub = lane >> lpr_log2;
     const int col0 = blockIdx.y * (LPR * VEC * P);
 
-    float acc[P][VEC], cen[P][VEC];
+    double acc[P][VEC];
+    float cen[P][VEC];
     bool on[P];
     int64_t coff[P];
 #pragma unroll
@@ -179,11 +220,11 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
         coff[p] = col;
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
-            acc[p][e] = 0.f;
-            cen[p][e] = on[p] ? cent[(int64_t)k * D + col + e] : 0.f;
+            acc[p][e] = 0.0;
+            cen[p][e] = (FULL && on[p]) ? cent[(int64_t)k * D + col + e] : 0.f;
         }
     }
-    float inert = 0.f;
+    double inert = 0.0, xsq = 0.0;
     const int per_warp = (nrows + 7) >> 3;
     const int wb = warp * per_warp;
     const int we = min(nrows, wb + per_warp);
@@ -209,16 +250,22 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 if (ok[u]) {
+                    float din = 0.f, dsq = 0.f;          // this lane's share of one row: at most 16 terms in fp32
 #pragma unroll
                     for (int p = 0; p < P; ++p)
                         if (on[p]) {
 #pragma unroll
                             for (int e = 0; e < VEC; ++e) {
-                                acc[p][e] += v[u][p].v[e];
-                                const float t = v[u][p].v[e] - cen[p][e];
-                                inert = fmaf(t, t, inert);
+                                const float xv = v[u][p].v[e];
+                                acc[p][e] += (double)xv;
+                                if (FULL) {
+                                    const float t = xv - cen[p][e];
+                                    din = fmaf(t, t, din);
+                                    dsq = fmaf(xv, xv, dsq);
+                                }
                             }
                         }
+                    if (FULL) { inert += (double)din; xsq += (double)dsq; }
                 }
             }
         }
@@ -236,8 +283,10 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
 #pragma unroll
             for (int e = 0; e < VEC; ++e) red[warp][(p * LPR + cl) * VEC + e] = acc[p][e];
     }
-    const double in_w = warp_sum((double)inert);
-    if (lane == 0) red_in[warp] = in_w;
+    if (FULL) {
+        const double in_w = warp_sum(inert), sq_w = warp_sum(xsq);
+        if (lane == 0) { red_in[warp][0] = in_w; red_in[warp][1] = sq_w; }
+    }
     __syncthreads();
     const int ncols = LPR * VEC * P;
     for (int cidx = threadIdx.x; cidx < ncols; cidx += blockDim.x) {
@@ -245,29 +294,29 @@ segsum_kernel(const float* __restrict__ x, int D, int K, const float* __restrict
         if (col < D) {
             double s = 0.0;
 #pragma unroll
-            for (int w = 0; w < 8; ++w) s += (double)red[w][cidx];
-            atomicAdd(partials + (int64_t)k * D + col, s);
+            for (int w = 0; w < 8; ++w) s += red[w][cidx];
+            atomicAdd(sums + (int64_t)k * D + col, sign * s);
         }
     }
-    if (threadIdx.x == 0) {
+    if (FULL && threadIdx.x < 2) {
         double s = 0.0;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) s += red_in[w];
-        atomicAdd(partials + (int64_t)K * D + K, s);
+        for (int w = 0; w < 8; ++w) s += red_in[w][threadIdx.x];
+        atomicAdd(scalars + threadIdx.x, s);       // [0] inertia, [1] sum |x|^2
     }
 }
 
-int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, int64_t r1, int chunk,
-                             cudaStream_t s) {
+// Sort the rows of `rs` by label into `perm` and add sign * (their per-cluster sums) to sums[K*D], sign * counts
+// to counts[K]; full: inertia and sum |x|^2 to scalars[0], scalars[1].  `slot` selects the sort scratch.
+static int sorted_accumulate(kmc_ctx* c, const RowSet& rs, int32_t* perm, int slot, double* sums, double* counts,
+                             double* scalars, double sign, bool full, cudaStream_t s) {
     const int K = (int)c->K, D = (int)c->D;
-    const int64_t n = r1 - r0;                       // rows of this chunk
+    const int64_t n = rs.n;                          // rows (upper bound for a device-counted list)
     if (n <= 0) return 0;
-    const int32_t* labels = labels_all + r0;
-    int32_t* perm = c->perm() + r0;                  // the chunk's own segment of the permutation
-    unsigned int* hist = c->sort_hist(chunk);
-    unsigned int* cursor = c->sort_cur(chunk);
-    unsigned int* offsets = c->sort_off(chunk);
-    unsigned int* segoff = c->sort_seg(chunk);
+    unsigned int* hist = c->sort_hist(slot);
+    unsigned int* cursor = c->sort_cur(slot);
+    unsigned int* offsets = c->sort_off(slot);
+    unsigned int* segoff = c->sort_seg(slot);
     // hist and cursor are adjacent in the workspace: one memset clears both
     KMC_CUDA(cudaMemsetAsync(hist, 0, (size_t)c->sort_offsets, s));
 
@@ -279,10 +328,10 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, 
         const size_t sm = hist_smem_ok ? (size_t)K * 4 : 0;
         if (sm > 48 * 1024)
             KMC_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        hist_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, n, K, hist, hist_smem_ok);
+        hist_kernel<<<(unsigned)blocks, 256, sm, s>>>(rs, K, hist, hist_smem_ok);
         KMC_CUDA(cudaGetLastError());
     }
-    scan_kernel<<<1, 1024, 0, s>>>(hist, K, offsets, segoff, c->partials() + (int64_t)K * D);
+    scan_kernel<<<1, 1024, 0, s>>>(hist, K, offsets, segoff, counts, sign, rs.gate, rs.gate_want);
     KMC_CUDA(cudaGetLastError());
     {
         const int sc_smem_ok = (size_t)K * 8 <= 192 * 1024;
@@ -290,10 +339,8 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, 
         const int64_t blocks = (n + kScatterChunk - 1) / kScatterChunk;
         if (sm > 48 * 1024)
             KMC_CUDA(cudaFuncSetAttribute(scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        if (blocks > 0) {
-            scatter_kernel<<<(unsigned)blocks, 256, sm, s>>>(labels, n, K, offsets, cursor, perm, sc_smem_ok, r0);
-            KMC_CUDA(cudaGetLastError());
-        }
+        scatter_kernel<<<(unsigned)blocks, 256, sm, s>>>(rs, K, offsets, cursor, perm, sc_smem_ok);
+        KMC_CUDA(cudaGetLastError());
     }
     {
         const bool vec4 = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(c->points) & 15) == 0);
@@ -307,18 +354,146 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, 
         const unsigned gy = (unsigned)((D + cols_per_block - 1) / cols_per_block);
         const int64_t gx = (n + kSegRows - 1) / kSegRows + K;
         dim3 grid((unsigned)gx, gy);
-#define KMC_SEGSUM(V, PP)                                                                                  \
-    segsum_kernel<V, PP><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), perm, offsets, segoff, \
-                                              c->partials(), lpr_log2)
+#define KMC_SEGSUM2(V, PP, F)                                                                                   \
+    segsum_kernel<V, PP, F><<<grid, 256, 0, s>>>(c->points, D, K, c->centroids(), perm, offsets, segoff, sums, \
+                                                 scalars, lpr_log2, sign, rs.gate, rs.gate_want)
+#define KMC_SEGSUM(V, PP) do { if (full) KMC_SEGSUM2(V, PP, true); else KMC_SEGSUM2(V, PP, false); } while (0)
         if (vec4) {
             if (passes == 1) KMC_SEGSUM(4, 1); else if (passes == 2) KMC_SEGSUM(4, 2); else KMC_SEGSUM(4, 4);
         } else {
             if (passes == 1) KMC_SEGSUM(1, 1); else if (passes == 2) KMC_SEGSUM(1, 2); else KMC_SEGSUM(1, 4);
         }
 #undef KMC_SEGSUM
+#undef KMC_SEGSUM2
         KMC_CUDA(cudaGetLastError());
     }
     c->launches += 4;
+    return 0;
+}
+
+// sums / counts / inertia / sum |x|^2 of rows [r0, r1), ADDED to the partial buffer; `gate`: see RowSet
+int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, int64_t r1, int chunk,
+                             const unsigned int* gate, cudaStream_t s) {
+    RowSet rs;
+    rs.labels = labels_all + r0; rs.rows = nullptr; rs.n = r1 - r0; rs.n_dev = nullptr; rs.row_base = r0;
+    rs.gate = gate; rs.gate_want = 1u;
+    double* part = c->partials();
+    return sorted_accumulate(c, rs, c->perm() + r0, chunk, part, part + c->K * c->D, part + c->K * c->D + c->K, 1.0, true, s);
+}
+
+// ---- incremental pass ----------------------------------------------------------------------------
+// Rows whose label differs from the previous pass, in ascending order within a warp's 32 rows; the list holds
+// `cap` rows, the count keeps running beyond it (the gate below then asks for a full pass).
+__global__ void __launch_bounds__(256) diff_labels_kernel(const int32_t* __restrict__ cur, const int32_t* __restrict__ prev,
+                                                          int64_t n, int32_t* __restrict__ list, unsigned long long cap,
+                                                          unsigned long long* __restrict__ n_chg) {
+    const int lane = threadIdx.x & 31;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t base = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n; base += stride) {
+        const int64_t i = base + lane;
+        const bool chg = (i < n) && (cur[i] != prev[i]);
+        const unsigned m = __ballot_sync(0xffffffffu, chg);
+        if (m == 0u) continue;
+        unsigned long long pos = 0;
+        if (lane == 0) pos = atomicAdd(n_chg, (unsigned long long)__popc(m));
+        pos = __shfl_sync(0xffffffffu, pos, 0) + (unsigned long long)__popc(m & ((1u << lane) - 1u));
+        if (chg && pos < cap) list[pos] = (int32_t)i;
+    }
+}
+
+// full_flag = 1 and an empty list if more rows changed than the list holds, else full_flag = 0
+__global__ void delta_gate_kernel(DeviceStats* st, unsigned long long cap) {
+    const unsigned long long m = st->n_changed;
+    if (m > cap) { st->acc_full = 1u; st->n_changed_eff = 0ull; } else { st->acc_full = 0u; st->n_changed_eff = m; }
+}
+
+// After the two variants: a full pass leaves fresh sums in `part` -> they become the running state; an
+// incremental pass updated the running state -> it is copied into `part`, and the inertia follows from the sums.
+// Layout of both buffers: [K*D sums | K counts | inertia | sum |x|^2].
+__global__ void __launch_bounds__(256) delta_finish_kernel(double* __restrict__ part, double* __restrict__ run,
+                                                           const float* __restrict__ cent, int K, int D,
+                                                           const DeviceStats* __restrict__ st) {
+    __shared__ double red[8];
+    const int64_t KD = (int64_t)K * D, total = KD + K;
+    const bool full = st->acc_full != 0u;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    double acc = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        if (full) { run[i] = part[i]; continue; }
+        const double v = run[i];
+        part[i] = v;
+        if (i < KD) {
+            const double cnt = run[KD + i / D];
+            if (cnt > 0.0) {                                  // (an empty cluster may hold a NaN centroid)
+                const double cv = (double)cent[i];
+                acc += cv * (cnt * cv - 2.0 * v);
+            }
+        }
+    }
+    if (full) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) run[total + 1] = part[total + 1];
+        return;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < 8; ++w) s += red[w];
+        if (blockIdx.x == 0) { s += run[total + 1]; part[total + 1] = run[total + 1]; }
+        atomicAdd(part + total, s);
+    }
+}
+
+// The accumulation stage of kmc_accumulate for the paths that sort (SIMT, tensor): labels of this pass are in
+// c->labels(), those of the previous pass in c->labels_prev().  Leaves the partial buffer filled and swaps the
+// two label buffers.
+int launch_accumulate_stage(kmc_ctx* c, cudaStream_t s) {
+    const int64_t KD = c->K * c->D;
+    double* part = c->partials();
+    double* run = c->running();
+    DeviceStats* st = c->stats();
+    if (!c->delta_enabled || !c->delta_valid) {
+        KMC_TRY(launch_sorted_accumulate(c, c->labels(), 0, c->n, 0, nullptr, s));
+        if (c->delta_enabled) {
+            KMC_CUDA(cudaMemcpyAsync(run, part, (size_t)(KD + c->K + 2) * 8, cudaMemcpyDeviceToDevice, s));
+            c->delta_valid = true;
+        }
+        KMC_CUDA(cudaMemsetAsync(&st->n_changed, 0, sizeof(unsigned long long), s));
+        c->swap_labels();
+        return 0;
+    }
+    const unsigned long long cap = (unsigned long long)c->chg_cap;
+    KMC_CUDA(cudaMemsetAsync(&st->n_changed, 0, sizeof(unsigned long long), s));
+    {
+        int64_t blocks = (c->n + 256 * 8 - 1) / (256 * 8);
+        const int64_t bcap = (int64_t)c->sm_count * 8;
+        blocks = blocks > bcap ? bcap : (blocks < 1 ? 1 : blocks);
+        diff_labels_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->labels(), c->labels_prev(), c->n, c->changed(), cap, &st->n_changed);
+        KMC_CUDA(cudaGetLastError());
+        delta_gate_kernel<<<1, 1, 0, s>>>(st, cap);
+        KMC_CUDA(cudaGetLastError());
+        c->launches += 2;
+    }
+    if (c->chg_cap > 0) {
+        RowSet rs;
+        rs.rows = c->changed(); rs.n = c->chg_cap; rs.n_dev = &st->n_changed_eff; rs.row_base = 0;
+        rs.gate = &st->acc_full; rs.gate_want = 0u;
+        rs.labels = c->labels();           // + x under the new label
+        KMC_TRY(sorted_accumulate(c, rs, c->perm(), kMaxChunks, run, run + KD, nullptr, 1.0, false, s));
+        rs.labels = c->labels_prev();      // - x under the old one
+        KMC_TRY(sorted_accumulate(c, rs, c->perm(), kMaxChunks, run, run + KD, nullptr, -1.0, false, s));
+    }
+    KMC_TRY(launch_sorted_accumulate(c, c->labels(), 0, c->n, 0, &st->acc_full, s));
+    {
+        int64_t blocks = (KD + c->K + 255) / 256;
+        const int64_t bcap = (int64_t)c->sm_count * 4;
+        blocks = blocks > bcap ? bcap : blocks;
+        delta_finish_kernel<<<(unsigned)blocks, 256, 0, s>>>(part, run, c->centroids(), (int)c->K, (int)c->D, st);
+        KMC_CUDA(cudaGetLastError());
+        c->launches++;
+    }
+    c->swap_labels();
     return 0;
 }
 
@@ -399,19 +574,21 @@ extern "C" int kmc_cluster_sums_noalloc(int device, const float* dev_points, con
     KMC_CUDA(cudaMemsetAsync(sc->hist, 0, 2 * sizeof(unsigned int) * (size_t)kNoAllocMaxK, s));
     if (n_rows == 0) return 0;
 
+    RowSet rs;
+    rs.labels = dev_labels; rs.rows = nullptr; rs.n = n_rows; rs.n_dev = nullptr; rs.row_base = 0;
+    rs.gate = nullptr; rs.gate_want = 0u;
     {
         int64_t blocks = (n_rows + 256 * 16 - 1) / (256 * 16);
         const int64_t cap = (int64_t)g_noalloc_sms[device] * 8;
         blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
-        hist_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 4, s>>>(dev_labels, n_rows, Ki, sc->hist, 1);
+        hist_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 4, s>>>(rs, Ki, sc->hist, 1);
         KMC_CUDA(cudaGetLastError());
     }
-    scan_kernel<<<1, 1024, 0, s>>>(sc->hist, Ki, sc->offsets, sc->segoff, dev_partials + K * D);
+    scan_kernel<<<1, 1024, 0, s>>>(sc->hist, Ki, sc->offsets, sc->segoff, dev_partials + K * D, 1.0, nullptr, 0u);
     KMC_CUDA(cudaGetLastError());
     {
         const int64_t blocks = (n_rows + kScatterChunk - 1) / kScatterChunk;
-        scatter_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 8, s>>>(dev_labels, n_rows, Ki, sc->offsets, sc->cursor,
-                                                                    sc->perm, 1, 0);
+        scatter_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 8, s>>>(rs, Ki, sc->offsets, sc->cursor, sc->perm, 1);
         KMC_CUDA(cudaGetLastError());
     }
     {
@@ -425,8 +602,8 @@ extern "C" int kmc_cluster_sums_noalloc(int device, const float* dev_points, con
         const int cols_per_block = cols_per_pass * passes;
         dim3 grid((unsigned)((n_rows + kSegRows - 1) / kSegRows + K), (unsigned)((Di + cols_per_block - 1) / cols_per_block));
 #define KMC_SEGSUM_NA(V, PP)                                                                                 \
-    segsum_kernel<V, PP><<<grid, 256, 0, s>>>(dev_points, Di, Ki, dev_centroids, sc->perm, sc->offsets, sc->segoff, \
-                                              dev_partials, lpr_log2)
+    segsum_kernel<V, PP, true><<<grid, 256, 0, s>>>(dev_points, Di, Ki, dev_centroids, sc->perm, sc->offsets, sc->segoff, \
+                                                    dev_partials, dev_partials + K * D + K, lpr_log2, 1.0, nullptr, 0u)
         if (vec4) {
             if (passes == 1) KMC_SEGSUM_NA(4, 1); else if (passes == 2) KMC_SEGSUM_NA(4, 2); else KMC_SEGSUM_NA(4, 4);
         } else {

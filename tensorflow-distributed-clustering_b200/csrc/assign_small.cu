@@ -15,7 +15,6 @@
 // materialised [N,K,M] tensors), :237-242 (K x gather+mean) and :244-248 (CPU bincount, mean*count).
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
-#include <cstdlib>
 
 namespace kmc {
 
@@ -177,7 +176,7 @@ small_kernel(const float* __restrict__ x, int64_t n, const float* __restrict__ c
 }
 
 template <int D, int THREADS>
-static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s) {
+static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s) {
     const int K = (int)c->K;
     const size_t smem_c = (size_t)((K * D + 3) & ~3) * sizeof(float);
     const size_t smem_acc = (size_t)K * (D + 1) * THREADS * sizeof(float);
@@ -189,7 +188,6 @@ static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, cud
     int per_sm = (int)((200 * 1024) / (smem + 1024));
     const int want = 1024 / THREADS;
     per_sm = per_sm < 1 ? 1 : (per_sm > want ? want : per_sm);
-    if (const char* e = getenv("KMC_SMALL_CTAS")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;   // experiment knob
     const int64_t cap = (int64_t)c->sm_count * per_sm;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
@@ -201,7 +199,7 @@ static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, cud
     const uint32_t idx_mask = ~((1u << bits) - 1u);
     auto launch = [&](auto kern) -> int {
         KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<(unsigned)blocks, THREADS, smem, s>>>(c->points, c->n, c->centroids(), K, c->partials(), labels_out,
+        kern<<<(unsigned)blocks, THREADS, smem, s>>>(c->points, c->n, cent, K, c->partials(), labels_out,
                                                      vec_ok, idx_mask);
         KMC_CUDA(cudaGetLastError());
         c->launches++;
@@ -218,24 +216,24 @@ static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, cud
 }
 
 template <int D>
-static int launch_small_d(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s) {
+static int launch_small_d(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s) {
     // 256 threads per CTA when the private accumulator columns fit twice per SM, else 128
     const size_t acc256 = (size_t)c->K * (D + 1) * 256 * sizeof(float);
-    if (!accumulate || acc256 <= 96 * 1024) return launch_small_dt<D, kSmallThreads>(c, accumulate, labels_out, s);
-    return launch_small_dt<D, 128>(c, accumulate, labels_out, s);
+    if (!accumulate || acc256 <= 96 * 1024) return launch_small_dt<D, kSmallThreads>(c, accumulate, labels_out, cent, s);
+    return launch_small_dt<D, 128>(c, accumulate, labels_out, cent, s);
 }
 
-int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s) {
+int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s) {
     if (!accumulate && !labels_out) return 0;
     switch ((int)c->D) {
-        case 1: return launch_small_d<1>(c, accumulate, labels_out, s);
-        case 2: return launch_small_d<2>(c, accumulate, labels_out, s);
-        case 3: return launch_small_d<3>(c, accumulate, labels_out, s);
-        case 4: return launch_small_d<4>(c, accumulate, labels_out, s);
-        case 5: return launch_small_d<5>(c, accumulate, labels_out, s);
-        case 6: return launch_small_d<6>(c, accumulate, labels_out, s);
-        case 7: return launch_small_d<7>(c, accumulate, labels_out, s);
-        case 8: return launch_small_d<8>(c, accumulate, labels_out, s);
+        case 1: return launch_small_d<1>(c, accumulate, labels_out, cent, s);
+        case 2: return launch_small_d<2>(c, accumulate, labels_out, cent, s);
+        case 3: return launch_small_d<3>(c, accumulate, labels_out, cent, s);
+        case 4: return launch_small_d<4>(c, accumulate, labels_out, cent, s);
+        case 5: return launch_small_d<5>(c, accumulate, labels_out, cent, s);
+        case 6: return launch_small_d<6>(c, accumulate, labels_out, cent, s);
+        case 7: return launch_small_d<7>(c, accumulate, labels_out, cent, s);
+        case 8: return launch_small_d<8>(c, accumulate, labels_out, cent, s);
         default: KMC_FAIL(KMC_E_UNSUPPORTED, "small path needs 1 <= D <= 8 (got %lld)", (long long)c->D);
     }
 }

@@ -30,7 +30,6 @@
 // distance computation a dense contraction.
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
-#include <cstdlib>
 #include <type_traits>
 
 namespace kmc {
@@ -792,7 +791,9 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
     pp.use_bias_mma = 0;
     if (p.scores) return launch(tc_assign_kernel<KC, true, 3, 8, false>, TcCfg<KC, 3>::kSmemBytes, pp);
     if (terms != 1) return launch(tc_assign_kernel<KC, false, 3, 8, false>, TcCfg<KC, 3>::kSmemBytes, pp);
-    if (getenv("KMC_NO_BIAS_MMA")) return launch(tc_assign_kernel<KC, false, 1, 8, false>, TcCfg<KC, 1>::kSmemBytes, pp);
+#ifdef KMC_NO_BIAS_MMA      // A/B build: biases added by the epilogue (FADD per score) instead of the extra MMA step
+    return launch(tc_assign_kernel<KC, false, 1, 8, false>, TcCfg<KC, 1>::kSmemBytes, pp);
+#endif
     // one term: the variant that lets the MMA add the biases, and the plain one; the device runs exactly one
     pp.use_bias_mma = 1;
     KMC_TRY(launch(tc_assign_kernel<KC, false, 1, 8, true>, TcCfg<KC, 1>::kSmemBytes, pp));

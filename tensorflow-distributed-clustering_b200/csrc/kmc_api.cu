@@ -31,6 +31,8 @@ static void layout_workspace(kmc_ctx* c) {
     auto take = [&](int64_t bytes) { int64_t o = off; off = align256(off + bytes); return o; };
     c->off_stats = take(sizeof(DeviceStats));
     c->off_centroids = take(c->K * c->D * 4);
+    c->off_cprev = take(c->K * c->D * 4);
+    c->off_shift_slots = take(kUpdateMaxBlocks * 8);
     c->off_partials = take((c->K * c->D + c->K + 2) * 8);
     if (c->path != KMC_PATH_SMALL) {
         // counting-sort scratch, one block per row chunk: hist | cursor | offsets | segoff
@@ -38,9 +40,13 @@ static void layout_workspace(kmc_ctx* c) {
         c->sort_offsets = c->sort_cursor + align256(c->K * 4);
         c->sort_segoff = c->sort_offsets + align256((c->K + 1) * 4);
         c->sort_stride = c->sort_segoff + align256((c->K + 1) * 4);
-        c->off_sort = take(c->sort_stride * kMaxChunks);
+        c->off_sort = take(c->sort_stride * (kMaxChunks + 1));    // last slot: the incremental pass
         c->off_labels = take(c->n * 4);
+        c->off_labels2 = take(c->n * 4);
         c->off_perm = take(c->n * 4);
+        c->chg_cap = c->n / 4;
+        c->off_changed = take((c->chg_cap > 0 ? c->chg_cap : 1) * 4);
+        c->off_running = take((c->K * c->D + c->K + 2) * 8);
     }
     if (c->path == KMC_PATH_TC) {
         c->off_xnorm = take(c->n * 8);          // per row: |X'| and |X' - X'_hi|, both rounded up
@@ -134,7 +140,7 @@ static int prof_mark(kmc_ctx* c, int slot, int which, cudaStream_t s) {
 static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -1) {
     switch (c->path) {
         case KMC_PATH_SMALL:
-            return launch_small(c, false, labels, s);
+            return launch_small(c, false, labels, c->centroids(), s);
         case KMC_PATH_SIMT:
             KMC_TRY(launch_simt_assign(c, nullptr, nullptr, c->n, labels, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
@@ -243,7 +249,6 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
     }
     layout_workspace(c);
     if (path == KMC_PATH_TC) {
-        if (const char* e = getenv("KMC_TC_TERMS")) c->tc_terms = (e[0] == '1') ? 1 : (e[0] == '3' ? 3 : 0);
         // one tensor term + exact refine (fewer MMAs, less power, cheaper epilogue) whenever the refine pass
         // has its sorted neighbour lists; the choice is revisited from the refine counts
         c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->off_nbr >= 0) ? 1 : 3);
@@ -259,10 +264,7 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
             KMC_FAIL((int)(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)), "could not create streams / events");
         }
         for (int i = 0; i < 2 * kMaxChunks; ++i) c->amb_host[i] = 0;
-        // large shards: assign row chunk c+1 on the caller's stream while chunk c is refined and
-        // accumulated on the side stream (different bottlenecks: ALU/tensor pipe vs HBM)
-        c->n_chunks = (n_rows >= ((int64_t)1 << 22)) ? kMaxChunks : 1;
-        if (const char* e = getenv("KMC_CHUNKS")) { int v = atoi(e); c->n_chunks = v < 1 ? 1 : (v > kMaxChunks ? kMaxChunks : v); }
+        c->n_chunks = 1;      // KMC_PARAM_CHUNKS > 1: the refine of row chunk c runs on the side stream under the tensor kernel of chunk c+1
     }
     *out = c;
     return 0;
@@ -303,6 +305,8 @@ int kmc_bind_workspace(kmc_ctx* c, void* dev_workspace, int64_t bytes) {
     c->have_centroids = false;
     c->planes_ready = false;
     c->tmaps_ready = false;
+    c->delta_valid = false;
+    c->lab_cur = 0;
     return 0;
 }
 
@@ -316,6 +320,7 @@ int kmc_bind_points(kmc_ctx* c, const float* dev_points, void* stream) {
     c->points = dev_points;
     c->planes_ready = false;
     c->streaming = false;
+    c->delta_valid = false;
     if (c->path == KMC_PATH_TC) {
         KMC_CUDA(cudaMemsetAsync(&c->stats()->x_absmax_bits, 0, sizeof(unsigned int), s));
         KMC_TRY(launch_absmax(c, dev_points, c->n * c->D, &c->stats()->x_absmax_bits, s));
@@ -338,6 +343,7 @@ int kmc_bind_points_streamed(kmc_ctx* c, const float* dev_points, void* stream) 
     c->planes_ready = false;
     c->streaming = true;
     c->stream_rows = 0;
+    c->delta_valid = false;
     KMC_CUDA(cudaMemsetAsync(&c->stats()->x_absmax_bits, 0, sizeof(unsigned int), s));
     KMC_TRY(tc_setup_tensor_maps(c));
     return 0;
@@ -363,11 +369,18 @@ int kmc_accumulate_rows(kmc_ctx* c, int64_t r0, int64_t r1, void* stream) {
     KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
     KMC_TRY(tc_pass(c, c->labels(), r0, r1, 0, s));
     KMC_TRY(refine_worklist(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[0], s));
-    KMC_TRY(launch_sorted_accumulate(c, c->labels(), r0, r1, 0, s));
+    KMC_TRY(launch_sorted_accumulate(c, c->labels(), r0, r1, 0, nullptr, s));
     c->stream_rows = r1;
     if (r1 == c->n) {
         c->streaming = false;
         KMC_TRY(tc_policy_post(c, s));
+        // same state as after kmc_accumulate: the sums of all pieces become the running state
+        if (c->delta_enabled) {
+            KMC_CUDA(cudaMemcpyAsync(c->running(), c->partials(), (size_t)kmc_partials_len(c) * 8, cudaMemcpyDeviceToDevice, s));
+            c->delta_valid = true;
+        }
+        c->last_pass_host_full = true;
+        c->swap_labels();
     }
     return 0;
 }
@@ -409,7 +422,7 @@ int kmc_stage_points(kmc_ctx* c, float* dev_dst, const void* host_src, int src_d
             KMC_CUDA(cudaMemcpyAsync(dst, c->pinned[b], (size_t)ne * esz, cudaMemcpyHostToDevice, s));
         }
         if (src_dtype == KMC_DTYPE_F64) {
-            KMC_TRY(launch_convert_f64(static_cast<const double*>(c->dev_stage[b]), dev_dst + e0, ne, s));
+            KMC_TRY(launch_convert_f64(c, static_cast<const double*>(c->dev_stage[b]), dev_dst + e0, ne, s));
             c->launches++;
         }
         KMC_CUDA(cudaEventRecord(c->pinned_free[b], s));
@@ -453,6 +466,7 @@ int kmc_resize(kmc_ctx* c, int64_t n_rows) {
     c->points = nullptr;          // the next batch must be bound before use
     c->streaming = false;
     c->tmaps_ready = false;
+    c->delta_valid = false;
     return 0;
 }
 
@@ -471,50 +485,53 @@ static int accumulate_impl(kmc_ctx* c, void* stream, bool zero) {
     const int slot = c->prof_acc_n;
     KMC_TRY(prof_mark(c, slot, 0, s));
     if (c->path == KMC_PATH_SMALL) {
-        KMC_TRY(launch_small(c, true, nullptr, s));
+        KMC_TRY(launch_small(c, true, nullptr, c->centroids(), s));
         KMC_TRY(prof_mark(c, slot, 1, s));
         KMC_TRY(prof_mark(c, slot, 2, s));
-    } else if (c->path == KMC_PATH_TC && c->n_chunks > 1 && c->n >= 4 * kTcBlockM) {
-        // chunk-pipelined tensor path: the caller's stream runs the tensor kernel over one row chunk after
-        // the other; the side stream follows one chunk behind with the exact refine, the counting sort and
-        // the segmented sums of the finished chunk (its CTAs share the SMs with the persistent tensor CTAs)
-        KMC_TRY(ensure_planes(c, s));
-        KMC_TRY(prof_mark(c, slot, 0, s));
-        tc_policy_poll(c);
-        KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
-        KMC_CUDA(cudaEventRecord(c->side_go, s));                 // partials zeroed, centroid planes ready
-        KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->side_go, 0));
-        const int64_t tiles = (c->n + kTcBlockM - 1) / kTcBlockM;
-        const int64_t tiles_per_chunk = (tiles + c->n_chunks - 1) / c->n_chunks;
-        for (int ch = 0; ch < c->n_chunks; ++ch) {
-            const int64_t r0 = (int64_t)ch * tiles_per_chunk * kTcBlockM;
-            const int64_t r1 = (r0 + tiles_per_chunk * kTcBlockM < c->n) ? r0 + tiles_per_chunk * kTcBlockM : c->n;
-            if (r0 >= c->n) break;
-            KMC_TRY(tc_pass(c, c->labels(), r0, r1, ch, s));
-            static const bool refine_on_side = getenv("KMC_REFINE_MAIN") == nullptr;    // experiment knob
-            if (refine_on_side) {
+    } else {
+        if (c->path == KMC_PATH_TC && c->n_chunks > 1 && c->n >= 4 * kTcBlockM) {
+            // chunked tensor path: the caller's stream runs the tensor kernel over one row chunk after the other;
+            // the side stream follows one chunk behind with the exact refine of the finished chunk (gather
+            // latency there, tensor pipe here)
+            KMC_TRY(ensure_planes(c, s));
+            KMC_TRY(prof_mark(c, slot, 0, s));
+            tc_policy_poll(c);
+            KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
+            KMC_CUDA(cudaEventRecord(c->side_go, s));                 // centroid planes and neighbour lists ready
+            KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->side_go, 0));
+            const int64_t tiles = (c->n + kTcBlockM - 1) / kTcBlockM;
+            const int64_t tiles_per_chunk = (tiles + c->n_chunks - 1) / c->n_chunks;
+            for (int ch = 0; ch < c->n_chunks; ++ch) {
+                const int64_t r0 = (int64_t)ch * tiles_per_chunk * kTcBlockM;
+                const int64_t r1 = (r0 + tiles_per_chunk * kTcBlockM < c->n) ? r0 + tiles_per_chunk * kTcBlockM : c->n;
+                if (r0 >= c->n) break;
+                KMC_TRY(tc_pass(c, c->labels(), r0, r1, ch, s));
                 KMC_CUDA(cudaEventRecord(c->chunk_done[ch], s));
                 KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->chunk_done[ch], 0));
                 KMC_TRY(refine_worklist(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[ch], c->side_stream));
-            } else {
-                KMC_TRY(refine_worklist(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[ch], s));
-                KMC_CUDA(cudaEventRecord(c->chunk_done[ch], s));
-                KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->chunk_done[ch], 0));
             }
-            KMC_TRY(launch_sorted_accumulate(c, c->labels(), r0, r1, ch, c->side_stream));
+            KMC_TRY(prof_mark(c, slot, 1, s));                        // end of the last tensor kernel
+            KMC_CUDA(cudaEventRecord(c->side_done, c->side_stream));
+            KMC_CUDA(cudaStreamWaitEvent(s, c->side_done, 0));        // phase "refine" = its exposed tail
+            KMC_TRY(tc_policy_post(c, s));
+        } else {
+            KMC_TRY(assign_into(c, c->labels(), s, slot));
         }
-        KMC_TRY(prof_mark(c, slot, 1, s));                        // end of the last tensor kernel
         KMC_TRY(prof_mark(c, slot, 2, s));
-        KMC_CUDA(cudaEventRecord(c->side_done, c->side_stream));
-        KMC_CUDA(cudaStreamWaitEvent(s, c->side_done, 0));        // phase "accumulate" = the exposed tail
-        KMC_TRY(tc_policy_post(c, s));
-    } else {
-        KMC_TRY(assign_into(c, c->labels(), s, slot));
-        KMC_TRY(prof_mark(c, slot, 2, s));
-        KMC_TRY(launch_sorted_accumulate(c, c->labels(), 0, c->n, 0, s));
+        if (zero) {
+            c->last_pass_host_full = !(c->delta_enabled && c->delta_valid);
+            KMC_TRY(launch_accumulate_stage(c, s));
+        } else {
+            // a batch of an out-of-core pass: its sums join those of other batches, no running state to keep
+            KMC_TRY(launch_sorted_accumulate(c, c->labels(), 0, c->n, 0, nullptr, s));
+            c->delta_valid = false;
+            c->last_pass_host_full = true;
+            c->swap_labels();
+        }
     }
     KMC_TRY(prof_mark(c, slot, 3, s));
     if (c->profile) c->prof_acc_n++;
+    c->updated_since_acc = false;
     return 0;
 }
 
@@ -525,6 +542,7 @@ int kmc_update(kmc_ctx* c, void* stream) {
     const int slot = c->prof_upd_n;
     KMC_TRY(prof_mark(c, slot, 4, s));
     KMC_TRY(launch_update(c, s));
+    c->updated_since_acc = true;
     if (c->path == KMC_PATH_TC) {
         KMC_TRY(launch_prep_centroids(c, s));   // update_kernel refreshed c_absmax
         if (c->off_ccdist >= 0) KMC_TRY(launch_ccdist(c, s));
@@ -555,6 +573,8 @@ int kmc_read_stats(kmc_ctx* c, double* host_stats, void* stream) {
     host_stats[KMC_STAT_KERNEL_PATH] = (double)c->path;
     host_stats[KMC_STAT_LAUNCHES] = (double)c->launches;
     host_stats[KMC_STAT_X_SCALED_MAX] = (double)__builtin_bit_cast(float, st.x_absmax_bits) * (double)st.sigma_x;
+    host_stats[KMC_STAT_CHANGED] = c->last_pass_host_full ? (double)c->n : (double)st.n_changed;
+    host_stats[KMC_STAT_FULL_PASS] = (c->last_pass_host_full || st.acc_full) ? 1.0 : 0.0;
     return 0;
 }
 
@@ -590,6 +610,20 @@ int kmc_assign(kmc_ctx* c, int32_t* dev_labels, void* stream) {
     return assign_into(c, dev_labels, static_cast<cudaStream_t>(stream));
 }
 
+int kmc_last_labels(kmc_ctx* c, int32_t* dev_labels, void* stream) {
+    KMC_TRY(check_ready(c, true));
+    if (!dev_labels && c->n > 0) KMC_FAIL(KMC_E_INVALID, "null labels");
+    if (c->n == 0) return 0;
+    KMC_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (c->path != KMC_PATH_SMALL) {
+        KMC_CUDA(cudaMemcpyAsync(dev_labels, c->labels_prev(), (size_t)c->n * 4, cudaMemcpyDeviceToDevice, s));
+        return 0;
+    }
+    // the fused small-D kernel keeps no labels: one label-only pass against the centroids of that pass
+    return launch_small(c, false, dev_labels, c->updated_since_acc ? c->centroids_prev() : c->centroids(), s);
+}
+
 int kmc_labels_to_host(kmc_ctx* c, const int32_t* dev_labels, void* host_labels, int label_bytes, int64_t n_labels,
                        void* stream) {
     if (!c || (n_labels > 0 && (!dev_labels || !host_labels))) KMC_FAIL(KMC_E_INVALID, "null argument");
@@ -618,7 +652,7 @@ int kmc_labels_to_host(kmc_ctx* c, const int32_t* dev_labels, void* host_labels,
             const int64_t r0 = i * per, nr = chunk_len(i);
             const void* src = dev_labels + r0;
             if (label_bytes == 8) {
-                KMC_TRY(launch_widen_labels(dev_labels + r0, static_cast<long long*>(c->dev_stage[b]), nr, s));
+                KMC_TRY(launch_widen_labels(c, dev_labels + r0, static_cast<long long*>(c->dev_stage[b]), nr, s));
                 c->launches++;
                 src = c->dev_stage[b];
             }
@@ -664,6 +698,10 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             if (value < 1.0 || value > (double)kMaxChunks || value != (double)(int)value)
                 KMC_FAIL(KMC_E_INVALID, "row chunks must be an integer in 1..%d", kMaxChunks);
             c->n_chunks = (int)value;
+            return 0;
+        case KMC_PARAM_INCREMENTAL:
+            c->delta_enabled = value != 0.0;
+            c->delta_valid = false;
             return 0;
         case KMC_PARAM_PROFILE:
             c->profile = value != 0.0;

@@ -44,6 +44,7 @@ constexpr int kBiasPieces = 6;
 constexpr int kBiasCols = 16;     // fp16 columns of a bias-plane row (one K=16 MMA step, 32-byte swizzled rows)
 __device__ __constant__ const float kBiasConst[kBiasPieces] = {32768.f, 32768.f, 32768.f, 32768.f, 16.f, 0.0078125f};
 constexpr float kBiasMax = 2147483648.f;   // the plane is used only while max_k S*|c_k|^2 < 2^31
+constexpr int kUpdateMaxBlocks = 1024;   // CTAs of update_kernel (one shift2 slot each)
 constexpr int kMaxChunks = 4;    // row chunks of one accumulate pass (assign of chunk c+1 overlaps accumulate of chunk c)
 
 // Device-resident scalars written by kernels (all doubles / 64-bit so one memset clears them).
@@ -64,6 +65,12 @@ struct DeviceStats {
     // launch reads the previous slot to pick the kernel that fits the walk lengths (see refine.cu)
     unsigned long long walk_sum[2];
     unsigned long long walk_rows[2];
+    // incremental accumulation (accumulate.cu): rows whose label changed in the last pass, the part of them the
+    // changed-row list holds (0 when the pass fell back to a full one), and that decision
+    unsigned long long n_changed;
+    unsigned long long n_changed_eff;
+    unsigned int acc_full;
+    unsigned int upd_done;            // CTAs of the running update_kernel that have stored their shift2 slot
 };
 
 }  // namespace kmc
@@ -93,11 +100,20 @@ struct kmc_ctx {
     char* ws = nullptr;
     int64_t ws_bytes = 0;
     int64_t need_bytes = 0;
-    int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_perm = 0,
+    int64_t off_cprev = 0, off_shift_slots = 0;
+    bool updated_since_acc = false;     // kmc_update ran after the last accumulate (centroids_prev() is current)
+    int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_labels2 = 0, off_perm = 0,
+            off_changed = 0, off_running = 0,
             off_sort = 0, sort_stride = 0, sort_cursor = 0, sort_offsets = 0, sort_segoff = 0,
             off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0, off_ambmask = 0,
             off_ccdist = -1, off_nbr = -1;
     const float* points = nullptr;
+    // incremental accumulation: two label buffers (this pass / previous pass), running fp64 sums and counts
+    bool delta_enabled = true;          // KMC_PARAM_INCREMENTAL
+    bool delta_valid = false;           // the running sums match labels_prev()
+    bool last_pass_host_full = true;    // the last pass was a full one by the host's decision (no running state yet)
+    int lab_cur = 0;                    // which label buffer the next pass writes
+    int64_t chg_cap = 0;                // rows the changed-row list holds; more changed rows -> full pass
     bool have_centroids = false;
     bool planes_ready = false;
     bool streaming = false;             // kmc_bind_points_streamed: rows arrive in pieces (kmc_accumulate_rows)
@@ -124,10 +140,15 @@ struct kmc_ctx {
 
     template <typename T> T* at(int64_t off) const { return reinterpret_cast<T*>(ws + off); }
     float* centroids() const { return at<float>(off_centroids); }
+    float* centroids_prev() const { return at<float>(off_cprev); }
     double* partials() const { return at<double>(off_partials); }
     kmc::DeviceStats* stats() const { return at<kmc::DeviceStats>(off_stats); }
-    int32_t* labels() const { return at<int32_t>(off_labels); }
+    int32_t* labels() const { return at<int32_t>(lab_cur ? off_labels2 : off_labels); }        // written by the next pass
+    int32_t* labels_prev() const { return at<int32_t>(lab_cur ? off_labels : off_labels2); }   // labels of the last pass
+    void swap_labels() { lab_cur ^= 1; }
     int32_t* perm() const { return at<int32_t>(off_perm); }
+    int32_t* changed() const { return at<int32_t>(off_changed); }
+    double* running() const { return at<double>(off_running); }      // [K*D sums | K counts | unused | sum |x|^2]
     // per-chunk scratch of the counting sort: hist | cursor | offsets | segoff
     unsigned int* sort_hist(int chunk) const { return at<unsigned int>(off_sort + chunk * sort_stride); }
     unsigned int* sort_cur(int chunk) const { return at<unsigned int>(off_sort + chunk * sort_stride + sort_cursor); }
@@ -139,15 +160,15 @@ namespace kmc {
 
 // ---- kernels (one .cu each) -------------------------------------------------------------------
 // stage.cu
-int launch_convert_f64(const double* src, float* dst, int64_t count, cudaStream_t s);
+int launch_convert_f64(kmc_ctx* c, const double* src, float* dst, int64_t count, cudaStream_t s);
 int launch_gather_centroids(kmc_ctx* c, const int32_t* labels, float* out, cudaStream_t s);
-int launch_widen_labels(const int32_t* src, long long* dst, int64_t count, cudaStream_t s);
+int launch_widen_labels(kmc_ctx* c, const int32_t* src, long long* dst, int64_t count, cudaStream_t s);
 int launch_absmax(kmc_ctx* c, const float* x, int64_t count, unsigned int* out_bits, cudaStream_t s);
 int launch_split_points(kmc_ctx* c, cudaStream_t s);
 int launch_split_points_range(kmc_ctx* c, int64_t r0, int64_t r1, bool keep_scale, cudaStream_t s);
 // assign_small.cu
 bool small_path_supported(int64_t K, int64_t D);
-int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, cudaStream_t s);
+int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s);
 // assign_simt.cu
 int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long long* n_work_dev,
                        int64_t n_work_host, int32_t* labels_out, cudaStream_t s);
@@ -168,8 +189,12 @@ int launch_ccdist(kmc_ctx* c, cudaStream_t s);
 int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* n_work_dev,
                   cudaStream_t s);
 // accumulate.cu
-// sums / counts / inertia of rows [r0, r1), ADDED to the partial buffer; `chunk` selects the sort scratch
-int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, int64_t r0, int64_t r1, int chunk, cudaStream_t s);
+// sums / counts / inertia / sum |x|^2 of rows [r0, r1), ADDED to the partial buffer; `chunk` selects the sort
+// scratch; `gate` (may be null): device flag, the kernels run only if *gate == 1
+int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels, int64_t r0, int64_t r1, int chunk,
+                             const unsigned int* gate, cudaStream_t s);
+// accumulation stage of kmc_accumulate (labels of this pass in c->labels()): incremental where possible
+int launch_accumulate_stage(kmc_ctx* c, cudaStream_t s);
 // update.cu
 int launch_update(kmc_ctx* c, cudaStream_t s);
 int launch_prep_centroids(kmc_ctx* c, cudaStream_t s);

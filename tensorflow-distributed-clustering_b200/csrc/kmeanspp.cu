@@ -103,10 +103,15 @@ __global__ void __launch_bounds__(1024) pp_select_kernel(const float* __restrict
         s_before = run;
     }
     __syncthreads();
-    if (s_block < 0) {                       // degenerate (all distances zero) or rounding at the very end
-        if (tid == 0) { s_block = (total > 0.0) ? n_blocks - 1 : 0; s_before = (total > 0.0) ? total - block_sum[n_blocks - 1] : 0.0; }
-        __syncthreads();
+    // degenerate (all distances zero) or rounding at the very end.  The flag is read into a register before
+    // anyone rewrites it and the barriers below are taken by the whole CTA.
+    const bool degenerate = s_block < 0;
+    __syncthreads();
+    if (degenerate && tid == 0) {
+        s_block = (total > 0.0) ? n_blocks - 1 : 0;
+        s_before = (total > 0.0) ? total - block_sum[n_blocks - 1] : 0.0;
     }
+    __syncthreads();
     const int64_t base = (int64_t)s_block * kPPBlockRows;
     const int64_t row = base + tid;
     const double m = (row < n) ? (double)mind[row] : 0.0;

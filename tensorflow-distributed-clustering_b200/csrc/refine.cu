@@ -10,7 +10,6 @@
 // Part of the replacement of reference scripts/distribuitedClustering.py:221-234.
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
-#include <cstdlib>
 
 namespace kmc {
 
@@ -354,10 +353,8 @@ int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const un
     const int32_t* nbr = sorted ? c->at<int32_t>(c->off_nbr) : nullptr;
     if (sorted && c->D % 4 == 0 && c->D <= 256 && ((reinterpret_cast<uintptr_t>(c->points) & 15) == 0)) {
         const int nv = (int)((c->D / 4 + 7) / 8);
-        // KMC_PARAM_REFINE_KERNEL (or the environment variable KMC_REFINE_KERNEL, for A/B runs of whole
-        // programs) = 4 | 8 pins one kernel; default: both enqueued, the device picks
-        static const int env_pin = getenv("KMC_REFINE_KERNEL") ? atoi(getenv("KMC_REFINE_KERNEL")) : 0;
-        const int pin = c->refine_kernel ? c->refine_kernel : env_pin;
+        // KMC_PARAM_REFINE_KERNEL = 4 | 8 pins one kernel; default: both enqueued, the device picks
+        const int pin = c->refine_kernel;
         const int slot = (int)(c->refine_launches++ & 1u);
         KMC_CUDA(cudaMemsetAsync(&c->stats()->walk_sum[slot], 0, sizeof(unsigned long long), s));
         KMC_CUDA(cudaMemsetAsync(&c->stats()->walk_rows[slot], 0, sizeof(unsigned long long), s));

@@ -15,10 +15,10 @@ __global__ void __launch_bounds__(256) convert_f64_kernel(const double* __restri
     for (; i < count; i += stride) dst[i] = (float)src[i];
 }
 
-int launch_convert_f64(const double* src, float* dst, int64_t count, cudaStream_t s) {
+int launch_convert_f64(kmc_ctx* c, const double* src, float* dst, int64_t count, cudaStream_t s) {
     if (count <= 0) return 0;
     int64_t blocks = (count + 255) / 256;
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > (int64_t)c->sm_count * 16) blocks = (int64_t)c->sm_count * 16;
     convert_f64_kernel<<<(unsigned)blocks, 256, 0, s>>>(src, dst, count);
     KMC_CUDA(cudaGetLastError());
     return 0;
@@ -32,10 +32,10 @@ __global__ void __launch_bounds__(256) widen_labels_kernel(const int32_t* __rest
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) dst[i] = (long long)src[i];
 }
 
-int launch_widen_labels(const int32_t* src, long long* dst, int64_t count, cudaStream_t s) {
+int launch_widen_labels(kmc_ctx* c, const int32_t* src, long long* dst, int64_t count, cudaStream_t s) {
     if (count <= 0) return 0;
     int64_t blocks = (count + 255) / 256;
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > (int64_t)c->sm_count * 16) blocks = (int64_t)c->sm_count * 16;
     widen_labels_kernel<<<(unsigned)blocks, 256, 0, s>>>(src, dst, count);
     KMC_CUDA(cudaGetLastError());
     return 0;

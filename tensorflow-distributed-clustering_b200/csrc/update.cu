@@ -11,8 +11,10 @@
 
 namespace kmc {
 
-__global__ void __launch_bounds__(256) update_kernel(float* __restrict__ cent, const double* __restrict__ partials,
-                                                     int K, int D, int empty_nan, DeviceStats* stats) {
+__global__ void __launch_bounds__(256) update_kernel(float* __restrict__ cent, float* __restrict__ cent_prev,
+                                                     const double* __restrict__ partials,
+                                                     int K, int D, int empty_nan, DeviceStats* stats,
+                                                     double* __restrict__ shift_slots) {
     const int64_t total = (int64_t)K * D;
     double shift = 0.0;
     float amax = 0.f;
@@ -21,6 +23,7 @@ __global__ void __launch_bounds__(256) update_kernel(float* __restrict__ cent, c
         const int k = (int)(i / D);
         const double cnt = partials[total + k];
         const float old = cent[i];
+        cent_prev[i] = old;              // the centroids the last pass was assigned against (kmc_last_labels)
         float nw;
         if (cnt > 0.0) nw = (float)(partials[i] / cnt);
         else nw = empty_nan ? __int_as_float(0x7fc00000) : old;
@@ -29,24 +32,42 @@ __global__ void __launch_bounds__(256) update_kernel(float* __restrict__ cent, c
         if (d == d) shift += d * d;
         amax = fmaxf(amax, fabsf(nw));
     }
+    // shift2 in a fixed summation order (lanes by butterfly, warps and CTAs in index order, the last CTA to finish
+    // adds the per-CTA slots): every GPU computes bit-identical values from identical inputs, so ranks that test
+    // shift2 <= tol on their own take the same decision
+    __shared__ double wsum[8];
     shift = warp_sum(shift);
     amax = warp_max(amax);
     if ((threadIdx.x & 31) == 0) {
-        if (shift != 0.0) atomicAdd(&stats->shift2, shift);
+        wsum[threadIdx.x >> 5] = shift;
         if (amax > 0.f && amax < INFINITY) atomicMax(&stats->c_absmax_bits, __float_as_uint(amax));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < 8; ++w) s += wsum[w];
+        shift_slots[blockIdx.x] = s;
+        __threadfence();
+        if (atomicAdd(&stats->upd_done, 1u) == gridDim.x - 1) {
+            __threadfence();
+            double total = 0.0;
+            for (unsigned b = 0; b < gridDim.x; ++b) total += *(volatile double*)(shift_slots + b);
+            stats->shift2 = total;
+            stats->upd_done = 0u;
+        }
     }
 }
 
 int launch_update(kmc_ctx* c, cudaStream_t s) {
     const int64_t total = c->K * c->D;
     int64_t blocks = (total + 255) / 256;
-    const int64_t cap = (int64_t)c->sm_count * 4;
+    const int64_t cap = kUpdateMaxBlocks < (int64_t)c->sm_count * 4 ? kUpdateMaxBlocks : (int64_t)c->sm_count * 4;
     blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
-    // shift2 and c_absmax restart at zero for every update
-    KMC_CUDA(cudaMemsetAsync(&c->stats()->shift2, 0, sizeof(double), s));
+    // c_absmax restarts at zero for every update (shift2 is overwritten by the kernel)
     KMC_CUDA(cudaMemsetAsync(&c->stats()->c_absmax_bits, 0, sizeof(unsigned int), s));
-    update_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), c->partials(), (int)c->K, (int)c->D,
-                                                   (c->flags & KMC_EMPTY_NAN) ? 1 : 0, c->stats());
+    update_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), c->centroids_prev(), c->partials(), (int)c->K, (int)c->D,
+                                                   (c->flags & KMC_EMPTY_NAN) ? 1 : 0, c->stats(),
+                                                   c->at<double>(c->off_shift_slots));
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;

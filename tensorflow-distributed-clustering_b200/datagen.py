@@ -30,24 +30,42 @@ def blobs_numpy(n: int, d: int, k: int, seed: int, sigma: float = 1.0, spread: f
 
 
 def blobs_torch(n: int, d: int, k: int, seed: int, device, sigma: float = 1.0, spread: float = 10.0,
-                block_rows: int = 1 << 22, out=None, stream: int = 0):
-    """Device blobs, generated block by block straight into HBM (no host copy of the data).
+                block_rows: int = 1 << 20, out=None, row0: int = 0, kind: str = "blobs"):
+    """Rows [row0, row0 + n) of a device data set, generated straight into HBM (no host copy of the data).
 
-    `seed` fixes the blob centres; `stream` selects an independent stream of points around those same
-    centres (one per rank when a data set is generated shard by shard)."""
+    The data set is defined block by block: global block b (rows [b*block_rows, (b+1)*block_rows)) comes from a
+    generator seeded with (seed, b), so any shard of it -- whatever the number of ranks -- holds the same rows
+    as the corresponding slice of the single-GPU data set.  `kind`: "blobs" (a uniformly chosen centre +
+    N(0, sigma^2)) or "uniform" (U(-spread, spread)^d, no cluster structure: the hard case for the tensor
+    kernel's certification)."""
     import torch
 
     centers = torch.from_numpy(blob_centers(k, d, seed, spread)).to(device)
     X = out if out is not None else torch.empty((n, d), dtype=torch.float32, device=device)
     gen = torch.Generator(device=device)
-    for b, r0 in enumerate(range(0, n, block_rows)):
-        r1 = min(n, r0 + block_rows)
-        gen.manual_seed((int(seed) * 1000003 + int(stream)) * 1009 + b)
-        which = torch.randint(0, k, (r1 - r0,), generator=gen, device=device)
-        blk = X[r0:r1]
-        blk.normal_(0.0, sigma, generator=gen)
-        blk += centers[which]
-        del which
+    r_end = row0 + n
+    tmp = None
+    for b in range(row0 // block_rows, (r_end + block_rows - 1) // block_rows):
+        g0, g1 = b * block_rows, (b + 1) * block_rows
+        gen.manual_seed(int(seed) * 1000003 * 1009 + b)
+        lo, hi = max(g0, row0), min(g1, r_end)
+        whole = (lo == g0 and hi == g1)
+        if whole:
+            blk = X[lo - row0:hi - row0]
+        else:
+            if tmp is None:
+                tmp = torch.empty((block_rows, d), dtype=torch.float32, device=device)
+            blk = tmp
+        if kind == "uniform":
+            blk.uniform_(-spread, spread, generator=gen)
+        else:
+            which = torch.randint(0, k, (block_rows,), generator=gen, device=device)
+            blk.normal_(0.0, sigma, generator=gen)
+            blk += centers[which]
+            del which
+        if not whole:
+            X[lo - row0:hi - row0].copy_(tmp[lo - g0:hi - g0])
+    del tmp
     return X, centers
 
 

@@ -25,7 +25,8 @@ def _shard(pkg, X, K, device, path="auto", empty="keep"):
     return s
 
 
-def _check_iterations(pkg, X, C0, iters, device, path="auto", n_shards=1, form="diff", hist=None, tc_terms=None):
+def _check_iterations(pkg, X, C0, iters, device, path="auto", n_shards=1, form="diff", hist=None, tc_terms=None,
+                      params=()):
     """Run `iters` Lloyd iterations on the GPU, one C-ABI call per phase, checking every
     intermediate against the oracle (labels_t, counts_t, inertia_t vs C_t; C_{t+1})."""
     import torch
@@ -37,6 +38,8 @@ def _check_iterations(pkg, X, C0, iters, device, path="auto", n_shards=1, form="
         s.set_centroids(C0)
         if tc_terms is not None:
             s.set_param(pkg._lib.KMC_PARAM_TC_TERMS, tc_terms)
+        for pid, val in params:
+            s.set_param(pid, val)
     C = np.asarray(C0, dtype=np.float64)
     for t in range(iters):
         ref = oracle.lloyd_iteration(X, C, n_shards=n_shards, form=form) if hist is None else None
@@ -113,14 +116,15 @@ def test_tensor_path_with_one_and_three_mma_terms(n, d, k, terms, pkg, cuda_devi
 
 
 @pytest.mark.parametrize("chunks,terms", [(4, 1), (3, 3), (2, 0)])
-def test_chunk_pipelined_accumulate(chunks, terms, pkg, cuda_device, monkeypatch):
-    """Large shards are assigned chunk by chunk while the finished chunk is refined and accumulated on a
-    second stream; force that mode on a small shard and check every iteration against the oracle."""
-    monkeypatch.setenv("KMC_CHUNKS", str(chunks))
+def test_chunk_pipelined_accumulate(chunks, terms, pkg, cuda_device):
+    """KMC_PARAM_CHUNKS > 1: the shard is assigned chunk by chunk while the finished chunk is refined on a
+    second stream; check every iteration against the oracle, with and without the incremental accumulation."""
     n, d, k = 50_000 + 77, 128, 512
     X, _ = pkg.datagen.blobs_numpy(n, d, k // 4, seed=99)
-    stats = _check_iterations(pkg, X, X[:k].copy(), 3, cuda_device, path="tc", form="gemm", tc_terms=terms)
-    assert stats["path"] == "tc"
+    for inc in (1, 0):
+        stats = _check_iterations(pkg, X, X[:k].copy(), 3, cuda_device, path="tc", form="gemm", tc_terms=terms,
+                                  params=[(pkg._lib.KMC_PARAM_CHUNKS, chunks), (pkg._lib.KMC_PARAM_INCREMENTAL, inc)])
+        assert stats["path"] == "tc"
 
 
 def test_tensor_fallback_on_poorly_separated_data(pkg, cuda_device):
@@ -371,7 +375,17 @@ def test_drop_in_entry_point_matches_oracle(pkg, cuda_device):
     assert oracle.rel_err(res["end_center"], ref["end_center"]) <= RTOL
     assert len(oracle.label_mismatches(res["cluster_idx"], ref["cluster_idx"], ref["final_d1"], ref["final_d2"])) == 0
     assert abs(res["inertia"] - ref["history"][-1]["inertia"]) <= RTOL * ref["history"][-1]["inertia"]
-    assert np.array_equal(res["centroids"], res["cluster_idx"])                 # one GPU: last shard = all rows
+    # `centroids` (:279, :286): labels of the final iteration against the centroids BEFORE its update
+    assert res["centroids"].dtype == np.int64 and res["centroids"].shape == (20000,)
+    last = ref["history"][-1]
+    assert len(oracle.label_mismatches(res["centroids"], ref["centroids"], last["d1"], last["d2"])) == 0
+    # ... which differs from cluster_idx while labels still move: two iterations from a poor start
+    res2 = pkg.distribuited_k_means(X64, 8, ["/device:GPU:0"], C0, 2)
+    ref2 = oracle.run_lloyd(X, C0, 2)
+    assert (ref2["centroids"] != ref2["cluster_idx"]).sum() > 0
+    last2 = ref2["history"][-1]
+    assert len(oracle.label_mismatches(res2["centroids"], ref2["centroids"], last2["d1"], last2["d2"])) == 0
+    assert len(oracle.label_mismatches(res2["cluster_idx"], ref2["cluster_idx"], ref2["final_d1"], ref2["final_d2"])) == 0
     # HEAD's 4-positional form (:180): centres from seeded k-means++
     res4 = pkg.distribuited_k_means(X, 8, 1, 5, seed=3)
     assert res4["n_iter"] == 5 and res4["init_center"].shape == (8, 2)
@@ -450,3 +464,139 @@ def test_device_kmeanspp_matches_its_cpu_restatement(pkg, cuda_device):
     assert all((X == c).all(1).any() for c in a["init_center"])
     ref = oracle.run_lloyd(X, a["init_center"], 3)
     assert oracle.rel_err(a["end_center"], ref["end_center"]) <= RTOL
+
+
+@pytest.mark.parametrize("n,d,k,path", [(60_000, 64, 96, "tc"), (40_000, 128, 256, "tc"), (30_000, 20, 50, "simt"),
+                                         (9_000, 33, 65, "simt")])
+def test_incremental_accumulation_equals_full_passes(n, d, k, path, pkg, cuda_device):
+    """kmc_accumulate with running sums (changed rows only) against KMC_PARAM_INCREMENTAL = 0 (every pass sums
+    every row), iteration by iteration from C0 = X[0:K]: identical counts, sums to 1e-12, inertia to 1e-7, and
+    the number of changed rows the library reports equals the number of labels that moved."""
+    X, _ = pkg.datagen.blobs_numpy(n, d, max(2, k // 3), seed=n + d)
+    C0 = X[:k].copy()
+    inc = _shard(pkg, X, k, cuda_device, path=path)
+    full = _shard(pkg, X, k, cuda_device, path=path)
+    full.set_param(pkg._lib.KMC_PARAM_INCREMENTAL, 0)
+    for s in (inc, full):
+        s.set_centroids(C0)
+    prev = None
+    saw_incremental = False
+    for it in range(8):
+        for s in (inc, full):
+            s.accumulate()
+        a, b = inc.partials.cpu().numpy(), full.partials.cpu().numpy()
+        assert np.array_equal(a[k * d:k * d + k], b[k * d:k * d + k]), f"iteration {it}: counts"
+        assert oracle.rel_err(a[:k * d], b[:k * d]) <= 1e-12, (it, oracle.rel_err(a[:k * d], b[:k * d]))
+        assert abs(a[k * d + k] - b[k * d + k]) <= 1e-7 * b[k * d + k], (it, a[k * d + k], b[k * d + k])
+        lab = inc.last_labels().cpu().numpy()
+        assert np.array_equal(lab, full.last_labels().cpu().numpy())
+        st = inc.stats()
+        if prev is not None:
+            moved = int((lab != prev).sum())
+            assert st["changed_rows"] == moved, (it, st, moved)
+            assert st["full_pass"] == (moved > n // 4)
+            saw_incremental |= not st["full_pass"]
+        else:
+            assert st["full_pass"] and full.stats()["full_pass"]
+        prev = lab
+        for s in (inc, full):
+            s.update()
+        assert np.array_equal(inc.get_centroids(), full.get_centroids()) or \
+            oracle.rel_err(inc.get_centroids(), full.get_centroids()) <= 1e-7
+    assert saw_incremental
+    inc.close()
+    full.close()
+
+
+def test_incremental_accumulation_falls_back_when_most_labels_move(pkg, cuda_device):
+    """More than a quarter of the rows changing their label (new centroids set from outside) must make the
+    device take the full pass, and a later quiet iteration the incremental one again."""
+    n, d, k = 50_000, 64, 64
+    X, _ = pkg.datagen.blobs_numpy(n, d, 40, seed=31)
+    s = _shard(pkg, X, k, cuda_device, path="tc")
+    s.set_centroids(X[:k].copy())
+    s.accumulate(); s.update()
+    s.accumulate()
+    assert not s.stats()["full_pass"]
+    s.set_centroids(X[1000:1000 + k][::-1].copy())            # unrelated centroids: nearly every label changes
+    s.accumulate()
+    st = s.stats()
+    assert st["full_pass"] and st["changed_rows"] > n // 4
+    part = s.partials.cpu().numpy()
+    ref = oracle.lloyd_iteration(X, X[1000:1000 + k][::-1].astype(np.float64), form="diff")
+    assert np.abs(part[k * d:k * d + k] - ref["counts"]).sum() <= 2 * int(oracle.near_tie_mask(ref["d1"], ref["d2"], TIE_RTOL).sum())
+    assert abs(part[k * d + k] - ref["inertia"]) <= RTOL * ref["inertia"]
+    s.update()
+    s.accumulate()
+    assert not s.stats()["full_pass"]
+    s.close()
+
+
+def test_incremental_inertia_on_data_far_from_the_origin(pkg, cuda_device):
+    """The incremental pass derives the inertia from the sums (sum|x|^2 - 2 c.S + n|c|^2): with coordinates near
+    1000 and a spread of 0.5 that difference cancels nine digits, which the fp64 sums must carry."""
+    rng = np.random.default_rng(8)
+    n, d, k = 30_000, 32, 40
+    centers = 1000.0 + rng.normal(0.0, 4.0, size=(k, d))
+    X = (centers[rng.integers(0, k, n)] + rng.normal(0.0, 0.5, size=(n, d))).astype(np.float32)
+    s = _shard(pkg, X, k, cuda_device, path="simt")
+    s.set_centroids(X[:k].copy())
+    C = X[:k].astype(np.float64)
+    for it in range(5):
+        s.accumulate()
+        ref = oracle.lloyd_iteration(X, C, form="diff")
+        got = s.partials.cpu().numpy()[k * d + k]
+        assert abs(got - ref["inertia"]) <= RTOL * ref["inertia"], (it, got, ref["inertia"], s.stats())
+        s.update()
+        C = s.get_centroids().astype(np.float64)
+    assert not s.stats()["full_pass"]
+    s.close()
+
+
+def test_last_labels_on_every_path(pkg, cuda_device):
+    """kmc_last_labels: the labels of the last accumulate pass (against the pre-update centroids) on the small-D
+    path (recomputed from the saved centroids), the SIMT path and the tensor path."""
+    for n, d, k, path in [(20_000, 3, 16, "small"), (8_000, 20, 30, "simt"), (20_000, 64, 64, "tc")]:
+        X, _ = pkg.datagen.blobs_numpy(n, d, max(2, k // 2), seed=d)
+        C0 = X[:k].copy()
+        s = _shard(pkg, X, k, cuda_device, path=path)
+        s.set_centroids(C0)
+        C = C0.astype(np.float64)
+        for it in range(2):
+            s.accumulate()
+            ref, d1, d2 = oracle.assign(X, C)
+            before = s.last_labels().cpu().numpy()                  # before the update
+            assert len(oracle.label_mismatches(before, ref, d1, d2, TIE_RTOL)) == 0, (path, it)
+            s.update()
+            after = s.last_labels().cpu().numpy()                   # after it: still the same pass
+            assert np.array_equal(before, after), (path, it)
+            C = s.get_centroids().astype(np.float64)
+        s.close()
+
+
+def test_gpu_mirror_matches_the_numpy_oracle(pkg, cuda_device):
+    """oracle/gpu_mirror.py (float64 torch on the GPU, used for the full-size checks of bench.py) against the
+    NumPy oracle it restates: identical labels outside near-ties, distances, sums, counts and inertia."""
+    import torch
+    from oracle import gpu_mirror
+
+    for n, d, k, form in [(20_000, 2, 8, "diff"), (9_000, 32, 256, "diff"), (5_000, 128, 1024, "gemm"), (300, 3, 1, "diff")]:
+        X, _ = pkg.datagen.blobs_numpy(n, d, max(1, k // 2), seed=n)
+        C = X[:k].astype(np.float64)
+        if k > 2:
+            C[2] = C[1]                                              # an exact tie: lowest index must win
+        ref = oracle.lloyd_iteration(X, C, form=form)
+        got = gpu_mirror.lloyd_pass_f64(torch.from_numpy(X).to(cuda_device), torch.from_numpy(C).to(cuda_device), chunk_rows=4096)
+        lab = got["labels"].cpu().numpy()
+        assert len(oracle.label_mismatches(lab, ref["labels"], ref["d1"], ref["d2"], TIE_RTOL)) == 0
+        exact_tie = ref["d1"] == ref["d2"]
+        assert np.array_equal(lab[exact_tie], ref["labels"][exact_tie])
+        assert np.allclose(got["d1"].cpu().numpy(), ref["d1"], rtol=1e-9, atol=1e-9 * float(ref["d1"].max()))
+        same = lab == ref["labels"]
+        assert oracle.rel_err(got["sums"].cpu().numpy(), ref["sums"]) <= 1e-6 + 1e-3 * (~same).mean()
+        assert np.abs(got["counts"].cpu().numpy() - ref["counts"]).sum() <= 2 * (~same).sum()
+        assert abs(float(got["inertia"]) - ref["inertia"]) <= 1e-9 * ref["inertia"]
+        cmp = gpu_mirror.compare_pass(got, torch.from_numpy(ref["labels"]).to(cuda_device),
+                                      torch.from_numpy(ref["sums"]).to(cuda_device),
+                                      torch.from_numpy(ref["counts"]).to(cuda_device), ref["inertia"])
+        assert cmp["label_mismatches_outside_near_ties"] == 0 and cmp["inertia_rel_err"] <= 1e-9
