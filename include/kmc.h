@@ -235,6 +235,8 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
                                    chunk c+1; 1 (default) = strictly one kernel after the other */
 #define KMC_PARAM_INCREMENTAL 6 /* 1 (default): kmc_accumulate updates running sums with the changed rows only where
                                    it can (see kmc_accumulate); 0: every pass sums every row */
+#define KMC_PARAM_TC_PAIR   7   /* tensor path, 1-term kernel: 1 (default) = CTA pairs share every MMA (cta_group::2,
+                                   M = 256: each SM stages half of every centroid tile); 0 = one CTA per MMA */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 
 /*

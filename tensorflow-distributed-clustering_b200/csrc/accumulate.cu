@@ -118,14 +118,14 @@ __global__ void __launch_bounds__(1024) scan_kernel(const unsigned int* __restri
 // ---- scatter: perm[offsets[l] + rank] = row ----------------------------------------------------
 __global__ void __launch_bounds__(256) scatter_kernel(const RowSet rs, int K, const unsigned int* __restrict__ offsets,
                                                       unsigned int* __restrict__ cursor,
-                                                      int32_t* __restrict__ perm, int use_smem) {
+                                                      int32_t* __restrict__ perm, int use_smem, int rows_per_cta) {
     extern __shared__ unsigned int sm[];
     if (rs.off()) return;
     const int64_t n = rs.count();
     unsigned int* lcnt = sm;        // [K] local counts, then local cursors
     unsigned int* lbase = sm + K;   // [K] global position of this CTA's first row of each cluster
-    const int64_t r0 = (int64_t)blockIdx.x * kScatterChunk;
-    const int64_t r1 = min(n, r0 + (int64_t)kScatterChunk);
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+    const int64_t r1 = min(n, r0 + (int64_t)rows_per_cta);
     if (r0 >= r1) return;
     if (!use_smem) {
         for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
@@ -336,10 +336,12 @@ static int sorted_accumulate(kmc_ctx* c, const RowSet& rs, int32_t* perm, int sl
     {
         const int sc_smem_ok = (size_t)K * 8 <= 192 * 1024;
         const size_t sm = sc_smem_ok ? (size_t)K * 8 : 0;
-        const int64_t blocks = (n + kScatterChunk - 1) / kScatterChunk;
+        // a row list is short and its labels are gathered (latency-bound): fewer rows per CTA, more CTAs at work
+        const int per_cta = rs.rows ? (K <= 2048 ? 2048 : kScatterChunk / 2) : kScatterChunk;
+        const int64_t blocks = (n + per_cta - 1) / per_cta;
         if (sm > 48 * 1024)
             KMC_CUDA(cudaFuncSetAttribute(scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        scatter_kernel<<<(unsigned)blocks, 256, sm, s>>>(rs, K, offsets, cursor, perm, sc_smem_ok);
+        scatter_kernel<<<(unsigned)blocks, 256, sm, s>>>(rs, K, offsets, cursor, perm, sc_smem_ok, per_cta);
         KMC_CUDA(cudaGetLastError());
     }
     {
@@ -387,17 +389,39 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, 
 __global__ void __launch_bounds__(256) diff_labels_kernel(const int32_t* __restrict__ cur, const int32_t* __restrict__ prev,
                                                           int64_t n, int32_t* __restrict__ list, unsigned long long cap,
                                                           unsigned long long* __restrict__ n_chg) {
+    // a warp compares 128 consecutive rows per step: one 16-byte load per lane and label array (both label
+    // buffers are 256-byte aligned workspace regions)
     const int lane = threadIdx.x & 31;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t base = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n; base += stride) {
-        const int64_t i = base + lane;
-        const bool chg = (i < n) && (cur[i] != prev[i]);
-        const unsigned m = __ballot_sync(0xffffffffu, chg);
-        if (m == 0u) continue;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t base = warp * 128; base < n; base += nwarps * 128) {
+        const int64_t i0 = base + 4 * lane;
+        unsigned bits = 0;
+        if (i0 + 3 < n) {
+            const int4 a = *reinterpret_cast<const int4*>(cur + i0), b = *reinterpret_cast<const int4*>(prev + i0);
+            bits = (a.x != b.x ? 1u : 0u) | (a.y != b.y ? 2u : 0u) | (a.z != b.z ? 4u : 0u) | (a.w != b.w ? 8u : 0u);
+        } else {
+            for (int e = 0; e < 4; ++e)
+                if (i0 + e < n && cur[i0 + e] != prev[i0 + e]) bits |= 1u << e;
+        }
+        if (__ballot_sync(0xffffffffu, bits != 0u) == 0u) continue;
+        const int cnt = __popc(bits);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
         unsigned long long pos = 0;
-        if (lane == 0) pos = atomicAdd(n_chg, (unsigned long long)__popc(m));
-        pos = __shfl_sync(0xffffffffu, pos, 0) + (unsigned long long)__popc(m & ((1u << lane) - 1u));
-        if (chg && pos < cap) list[pos] = (int32_t)i;
+        if (lane == 0) pos = atomicAdd(n_chg, (unsigned long long)total);
+        pos = __shfl_sync(0xffffffffu, pos, 0) + (unsigned long long)(incl - cnt);
+        while (bits) {
+            const int e = __ffs(bits) - 1;
+            bits &= bits - 1u;
+            if (pos < cap) list[pos] = (int32_t)(i0 + e);
+            ++pos;
+        }
     }
 }
 
@@ -466,7 +490,7 @@ int launch_accumulate_stage(kmc_ctx* c, cudaStream_t s) {
     const unsigned long long cap = (unsigned long long)c->chg_cap;
     KMC_CUDA(cudaMemsetAsync(&st->n_changed, 0, sizeof(unsigned long long), s));
     {
-        int64_t blocks = (c->n + 256 * 8 - 1) / (256 * 8);
+        int64_t blocks = (c->n + 256 * 16 - 1) / (256 * 16);
         const int64_t bcap = (int64_t)c->sm_count * 8;
         blocks = blocks > bcap ? bcap : (blocks < 1 ? 1 : blocks);
         diff_labels_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->labels(), c->labels_prev(), c->n, c->changed(), cap, &st->n_changed);
@@ -588,7 +612,7 @@ extern "C" int kmc_cluster_sums_noalloc(int device, const float* dev_points, con
     KMC_CUDA(cudaGetLastError());
     {
         const int64_t blocks = (n_rows + kScatterChunk - 1) / kScatterChunk;
-        scatter_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 8, s>>>(rs, Ki, sc->offsets, sc->cursor, sc->perm, 1);
+        scatter_kernel<<<(unsigned)blocks, 256, (size_t)Ki * 8, s>>>(rs, Ki, sc->offsets, sc->cursor, sc->perm, 1, kScatterChunk);
         KMC_CUDA(cudaGetLastError());
     }
     {

@@ -40,6 +40,8 @@ constexpr uint32_t kBiasStageBytes = kTcBlockN * kBiasCols * 2;   // 256 rows x 
 constexpr uint32_t kTmemCols = 512;
 // kind::f16, fp16 x fp16 -> fp32, A and B K-major, M = 128, N = 256
 constexpr uint32_t kInstrDesc = (1u << 4) | ((uint32_t)(kTcBlockN >> 3) << 17) | ((uint32_t)(kTcBlockM >> 4) << 24);
+// ... and M = 256 for the MMA a CTA pair shares (cta_group::2)
+constexpr uint32_t kInstrDescPair = (1u << 4) | ((uint32_t)(kTcBlockN >> 3) << 17) | ((uint32_t)((2 * kTcBlockM) >> 4) << 24);
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
 constexpr float kPackRel = 1.6e-5f;                 // > 2^-16: relative weight of the 7 packed index bits
@@ -84,13 +86,18 @@ struct TcParams {
 
 // Shared-memory plan.  With one MMA term only the hi plane of the points is staged, which leaves
 // room on the SM for the CTAs of the accumulation kernels that run concurrently on the side stream.
-template <int KC, int NPASS> struct TcCfg {
+// NCTA = 2: a CTA pair shares every MMA (cta_group::2, M = 256): each CTA stages its own 128 rows of points and
+// HALF of every centroid stage (128 centroids x 64 columns, 16 KB), so an SM pulls half the centroid bytes
+// from L2 and its tensor core reads half the B bytes from shared memory per score.
+template <int KC, int NPASS, int NCTA = 1> struct TcCfg {
     static constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
+    static constexpr uint32_t kStageB = kStageBytesB / NCTA;          // bytes of one B stage in THIS CTA
+    static constexpr uint32_t kBiasStage = kBiasStageBytes / NCTA;
 #ifndef KMC_TC_STAGES1
 #define KMC_TC_STAGES1 3
 #endif
-    static constexpr int kStages = (NPASS == 1) ? KMC_TC_STAGES1 : ((KC == 1) ? 4 : 3);
-    static constexpr uint32_t kBBytes = kStages * kStageBytesB;
+    static constexpr int kStages = (NCTA == 2) ? 6 : ((NPASS == 1) ? KMC_TC_STAGES1 : ((KC == 1) ? 4 : 3));
+    static constexpr uint32_t kBBytes = kStages * kStageB;
     // 1 term: a constant 128 x 16 fp16 tile (32-byte swizzled) holding kBiasConst in its first columns; multiplied
     // with a stage of the bias plane it makes the MMA add S*|c_k|^2 to the accumulator (no FADD per score in the
     // epilogue)
@@ -118,7 +125,11 @@ template <int KC, int NPASS> struct TcCfg {
 template <unsigned SLEEP_NS>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, DeviceStats* st, unsigned code) {
     if (mbar_try_wait(bar, parity)) return;
+#ifdef KMC_PAIR_SPIN
+    if (false) {
+#else
     if (SLEEP_NS) {
+#endif
         // single-thread roles: parked by the hardware between polls (suspend-time hint), no clock reads
         unsigned spins = 0;
         while (!mbar_try_wait_hint(bar, parity, KMC_WAIT_HINT_NS)) {
@@ -279,7 +290,7 @@ __device__ __forceinline__ void epi_chunk_part(const uint32_t (&r)[32], const fl
     for (int b = 0; b < 32 / kEpiG; b += 2) top2_pair(tb, bm[b], bm[b + 1]);
 }
 
-template <int KC, bool SCORES, int NPASS, int EW, bool AUG>   // EW = epilogue warps; AUG = bias through the MMA
+template <int KC, bool SCORES, int NPASS, int EW, bool AUG, int NCTA>   // EW = epilogue warps; AUG = bias through the MMA
 #ifndef KMC_TC_MAXNREG
 #define KMC_TC_MAXNREG 128
 #endif
@@ -287,7 +298,9 @@ __global__ void __maxnreg__(SCORES ? 128 : KMC_TC_MAXNREG)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_bias,
                  const TcParams p) {
-    using Cfg = TcCfg<KC, NPASS>;
+    using Cfg = TcCfg<KC, NPASS, NCTA>;
+    constexpr uint32_t kInstrDescT = (NCTA == 2) ? kInstrDescPair : kInstrDesc;
+    static_assert(NCTA == 1 || (NPASS == 1 && AUG && !SCORES), "the CTA-pair kernel exists for the 1-term AUG variant");
     if (p.gate_flag && *p.gate_flag == 0u) return;     // uniform for the whole grid
     // bias through the MMA (AUG): only with one term (shared memory for the extra tile) and while the fp16
     // pieces of the bias plane can represent every S*|c_k|^2.  That is a device-side fact, so the host launches
@@ -302,16 +315,23 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     auto a_full = [&](int i) { return bar0 + 8u * i; };
     auto a_empty = [&](int i) { return bar0 + 16u + 8u * i; };
     auto b_full = [&](int i) { return bar0 + 32u + 8u * i; };
-    auto b_empty = [&](int i) { return bar0 + 64u + 8u * i; };
-    auto t_full = [&](int i) { return bar0 + 96u + 8u * i; };
-    auto t_empty = [&](int i) { return bar0 + 112u + 8u * i; };
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::kBarOff + 128);
+    auto b_empty = [&](int i) { return bar0 + 32u + 8u * (Cfg::kStages + i); };
+    auto t_full = [&](int i) { return bar0 + 32u + 16u * Cfg::kStages + 8u * i; };
+    auto t_empty = [&](int i) { return bar0 + 48u + 16u * Cfg::kStages + 8u * i; };
+    static_assert(64 + 16 * Cfg::kStages + 8 <= 256, "barrier region");
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::kBarOff + 64 + 16 * Cfg::kStages);
 
+    // CTA pair: rank 0 (the leader) issues every MMA.  The "full" barriers of the operand stages and the "TMEM
+    // buffer released" barriers are used in the leader only (both CTAs' TMA bytes and both CTAs' epilogue warps
+    // arrive there); the "empty" and "accumulator ready" barriers exist in both CTAs and are signalled by the
+    // leader's multicast commits.
+    const uint32_t cta_rank = (NCTA == 2) ? cluster_ctarank() : 0u;
+    const bool leader = cta_rank == 0u;
     if (threadIdx.x == 0) {
         if (smem_base & 1023u) { p.stats->watchdog = 0xA11u; __trap(); }
         for (int i = 0; i < 2; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); }
         for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), EW); }
+        for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), EW * NCTA); }
         fence_barrier_init();
     }
     if (warp == 0 && lane == 0) {
@@ -320,8 +340,8 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         tma_prefetch_desc(&tm_c);
     }
     if (warp == 2) {
-        tmem_alloc(smem_u32(tmem_slot), kTmemCols);
-        tmem_relinquish();
+        if (NCTA == 2) { tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols); tmem_relinquish_pair(); }
+        else { tmem_alloc(smem_u32(tmem_slot), kTmemCols); tmem_relinquish(); }
     }
     if (AUG) {
         // constant A tile of the bias step (128 rows x 16 fp16), in the 32-byte-swizzled K-major layout TMA
@@ -338,26 +358,38 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     }
     tc_fence_before_sync();
     __syncthreads();
+    if (NCTA == 2) cluster_sync_all();          // the peer's barriers are initialised before anything arrives on them
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
-    const int n_my_tiles = (p.n_mtiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    // work units: 128-row tiles per CTA (NCTA = 1) or 256-row tile pairs per CTA pair (both CTAs of a pair walk
+    // the same number of units; the odd tile at the end is an out-of-range tile for rank 1: zero-filled loads,
+    // no rows written)
+    const int unit = (int)blockIdx.x / NCTA, n_units_grid = (int)gridDim.x / NCTA;
+    const int n_units = (p.n_mtiles + NCTA - 1) / NCTA;
+    const int n_my_tiles = (n_units - unit + n_units_grid - 1) / n_units_grid;
+    auto tile_of = [&](int it) { return p.tile0 + (unit + it * n_units_grid) * NCTA + (int)cta_rank; };
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             uint32_t sb = 0;
+            // one tile load: own shared memory, bytes counted on the leader's "full" barrier (pair) or our own
+            auto load_tile = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar, uint64_t policy) {
+                if (NCTA == 2) tma_load_2d_hint_pair(dst, tm, c0, c1, mapa_cluster(bar, 0u), policy);
+                else tma_load_2d_hint(dst, tm, c0, c1, bar, policy);
+            };
             auto load_a = [&](int it) {
                 const int abuf = it % Cfg::kABufs;
-                const int m0 = (p.tile0 + (int)blockIdx.x + it * (int)gridDim.x) * kTcBlockM;
+                const int m0 = tile_of(it) * kTcBlockM;
                 mbar_wait<200>(a_empty(abuf), (((uint32_t)it / Cfg::kABufs) & 1u) ^ 1u, p.stats, 0x100u + abuf);
-                mbar_arrive_expect_tx(a_full(abuf), (uint32_t)Cfg::kPlanes * KC * kTileBytesA);
+                if (leader) mbar_arrive_expect_tx(a_full(abuf), (uint32_t)NCTA * Cfg::kPlanes * KC * kTileBytesA);
 #pragma unroll
                 for (int pl = 0; pl < Cfg::kPlanes; ++pl)
 #pragma unroll
                     for (int kc = 0; kc < KC; ++kc)
-                        tma_load_2d_hint(smem_base + ((abuf * Cfg::kPlanes + pl) * KC + kc) * kTileBytesA,
-                                         pl == 0 ? &tm_xhi : &tm_xlo, kc * kTcChunkK, m0, a_full(abuf), kEvictFirst);
+                        load_tile(smem_base + ((abuf * Cfg::kPlanes + pl) * KC + kc) * kTileBytesA,
+                                  pl == 0 ? &tm_xhi : &tm_xlo, kc * kTcChunkK, m0, a_full(abuf), kEvictFirst);
             };
             load_a(0);
             for (int it = 0; it < n_my_tiles; ++it) {
@@ -365,9 +397,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     if (aug) {      // stage of the bias plane: 256 centroids x 16 columns (8 KB of the slot)
                         const int slot = sb % Cfg::kStages;
                         mbar_wait<100>(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x280u + slot);
-                        mbar_arrive_expect_tx(b_full(slot), kBiasStageBytes);
-                        tma_load_2d_hint(smem_base + Cfg::kABytes + slot * kStageBytesB, &tm_bias, 0, nt * kTcBlockN,
-                                         b_full(slot), kEvictLast);
+                        if (leader) mbar_arrive_expect_tx(b_full(slot), kBiasStageBytes);
+                        load_tile(smem_base + Cfg::kABytes + slot * Cfg::kStageB, &tm_bias, 0,
+                                  nt * kTcBlockN + (int)cta_rank * (kTcBlockN / NCTA), b_full(slot), kEvictLast);
                         ++sb;
                     }
                     for (int kc = 0; kc < KC; ++kc) {
@@ -375,9 +407,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         for (int pl = 0; pl < ((NPASS == 1) ? 1 : 2); ++pl) {
                             const int slot = sb % Cfg::kStages;
                             mbar_wait<100>(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x200u + slot);
-                            mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
-                            tma_load_2d_hint(smem_base + Cfg::kABytes + slot * kStageBytesB, &tm_c, kc * kTcChunkK,
-                                             pl * p.K_pad + nt * kTcBlockN, b_full(slot), kEvictLast);
+                            if (leader) mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
+                            load_tile(smem_base + Cfg::kABytes + slot * Cfg::kStageB, &tm_c, kc * kTcChunkK,
+                                      pl * p.K_pad + nt * kTcBlockN + (int)cta_rank * (kTcBlockN / NCTA), b_full(slot),
+                                      kEvictLast);
                             ++sb;
                         }
                     }
@@ -388,8 +421,14 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issuer (pair: the leader CTA only) =====================
+        auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t acc) {
+            if (NCTA == 2) umma_f16_pair(d, da, db, kInstrDescT, acc); else umma_f16(d, da, db, kInstrDescT, acc);
+        };
+        auto commit = [&](uint32_t bar) {
+            if (NCTA == 2) umma_commit_pair(bar, (uint16_t)3); else umma_commit(bar);
+        };
+        if (lane == 0 && leader) {
             uint32_t sb = 0, ac = 0;
             for (int it = 0; it < n_my_tiles; ++it) {
                 const int abuf = it % Cfg::kABufs;
@@ -407,10 +446,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         const int slot = sb % Cfg::kStages;
                         mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x580u + slot);
                         tc_fence_after_sync();
-                        umma_f16(d_tmem, umma_desc_sw32(smem_base + Cfg::kAExtOff),
-                                 umma_desc_sw32(smem_base + Cfg::kABytes + slot * kStageBytesB), kInstrDesc, 0);
+                        mma(d_tmem, umma_desc_sw32(smem_base + Cfg::kAExtOff),
+                            umma_desc_sw32(smem_base + Cfg::kABytes + slot * Cfg::kStageB), 0);
                         accum = 1;
-                        umma_commit(b_empty(slot));
+                        commit(b_empty(slot));
                         ++sb;
                     }
                     for (int kc = 0; kc < KC; ++kc) {
@@ -418,38 +457,38 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         int slot = sb % Cfg::kStages;
                         mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x500u + slot);
                         tc_fence_after_sync();
-                        uint32_t b_addr = smem_base + Cfg::kABytes + slot * kStageBytesB;
+                        uint32_t b_addr = smem_base + Cfg::kABytes + slot * Cfg::kStageB;
 #pragma unroll
                         for (int k4 = 0; k4 < 4; ++k4) {
-                            umma_f16(d_tmem, umma_desc_sw128(a_hi + kc * kTileBytesA + k4 * 32),
-                                     umma_desc_sw128(b_addr + k4 * 32), kInstrDesc, accum);
+                            mma(d_tmem, umma_desc_sw128(a_hi + kc * kTileBytesA + k4 * 32),
+                                umma_desc_sw128(b_addr + k4 * 32), accum);
                             accum = 1;
                         }
                         if (NPASS == 3) {
 #pragma unroll
                             for (int k4 = 0; k4 < 4; ++k4)
-                                umma_f16(d_tmem, umma_desc_sw128(a_lo + kc * kTileBytesA + k4 * 32),
-                                         umma_desc_sw128(b_addr + k4 * 32), kInstrDesc, 1);
+                                mma(d_tmem, umma_desc_sw128(a_lo + kc * kTileBytesA + k4 * 32),
+                                    umma_desc_sw128(b_addr + k4 * 32), 1);
                         }
-                        umma_commit(b_empty(slot));
+                        commit(b_empty(slot));
                         ++sb;
                         if (NPASS == 1) continue;
                         // stage with the centroid lo plane: x_hi*c_lo
                         slot = sb % Cfg::kStages;
                         mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x600u + slot);
                         tc_fence_after_sync();
-                        b_addr = smem_base + Cfg::kABytes + slot * kStageBytesB;
+                        b_addr = smem_base + Cfg::kABytes + slot * Cfg::kStageB;
 #pragma unroll
                         for (int k4 = 0; k4 < 4; ++k4)
-                            umma_f16(d_tmem, umma_desc_sw128(a_hi + kc * kTileBytesA + k4 * 32),
-                                     umma_desc_sw128(b_addr + k4 * 32), kInstrDesc, 1);
-                        umma_commit(b_empty(slot));
+                            mma(d_tmem, umma_desc_sw128(a_hi + kc * kTileBytesA + k4 * 32),
+                                umma_desc_sw128(b_addr + k4 * 32), 1);
+                        commit(b_empty(slot));
                         ++sb;
                     }
-                    umma_commit(t_full(buf));
+                    commit(t_full(buf));
                     KMC_TRACE_AT(ac, 7);
                 }
-                umma_commit(a_empty(abuf));
+                commit(a_empty(abuf));
             }
         }
     } else if (warp >= 4) {
@@ -470,9 +509,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         const float clomax = __uint_as_float(p.stats->c_lonormmax_bits);
         uint32_t ac = 0;
         // row norms of the NEXT row tile are fetched while the current one is scanned
-        auto tile_row = [&](int it) {
-            return ((int64_t)p.tile0 + blockIdx.x + (int64_t)it * gridDim.x) * kTcBlockM + q * 32 + lane;
-        };
+        auto tile_row = [&](int it) { return (int64_t)tile_of(it) * kTcBlockM + q * 32 + lane; };
+        // "TMEM buffer released": the leader's barrier, also for the warps of the peer CTA
+        const uint32_t t_empty_c[2] = {(NCTA == 2) ? mapa_cluster(t_empty(0), 0u) : t_empty(0),
+                                       (NCTA == 2) ? mapa_cluster(t_empty(1), 0u) : t_empty(1)};
         float2 nn_next = make_float2(0.f, 0.f);
         if (n_my_tiles > 0 && tile_row(0) < p.n) nn_next = *reinterpret_cast<const float2*>(p.xnorm + 2 * tile_row(0));
         for (int it = 0; it < n_my_tiles; ++it) {
@@ -547,7 +587,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 tc_fence_before_sync();
                 __syncwarp();
                 if (threadIdx.x == 128) KMC_TRACE_AT(ac, 3);
-                if (lane == 0) mbar_arrive(t_empty(buf));
+                if (lane == 0) {
+                    if (NCTA == 2 && !leader) mbar_arrive_cluster(t_empty_c[buf]); else mbar_arrive(t_empty(buf));
+                }
                 // a changed best value carries its column in the low bits
                 if (__float_as_uint(te.m1) != __float_as_uint(e_in)) a_e = kbase + (int)(__float_as_uint(te.m1) & 0x7Fu);
                 if (__float_as_uint(to.m1) != __float_as_uint(o_in)) a_o = kbase + (int)(__float_as_uint(to.m1) & 0x7Fu);
@@ -667,9 +709,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
 
     tc_fence_before_sync();
     __syncthreads();
+    if (NCTA == 2) cluster_sync_all();          // no CTA leaves (or frees TMEM) while its peer may still signal it
     if (warp == 2) {
         tc_fence_after_sync();
-        tmem_dealloc(tmem_base, kTmemCols);
+        if (NCTA == 2) tmem_dealloc_pair(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols);
     }
 }
 
@@ -709,6 +752,11 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
                      kTcBlockN));
     KMC_TRY(make_map(fn, &c->tmap_bias, c->at<void>(c->off_cbias), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN, kBiasCols,
                      CU_TENSOR_MAP_SWIZZLE_32B));
+    // CTA pairs: every CTA loads its half (128 centroids) of a stage
+    KMC_TRY(make_map(fn, &c->tmap_c_half, c->at<void>(c->off_cplanes), (uint64_t)c->D_pad, (uint64_t)(2 * c->K_pad),
+                     kTcBlockN / 2));
+    KMC_TRY(make_map(fn, &c->tmap_bias_half, c->at<void>(c->off_cbias), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN / 2,
+                     kBiasCols, CU_TENSOR_MAP_SWIZZLE_32B));
     c->tmaps_ready = true;
     return 0;
 }
@@ -787,17 +835,38 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
         c->launches++;
         return 0;
     };
+    // CTA pairs: clusters of two CTAs (one per SM of a TPC), the centroid maps with 128-row boxes
+    auto launch_pair = [&](auto kern, uint32_t smem_bytes, const TcParams& pp) -> int {
+        KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        const int pairs_needed = (p.n_mtiles + 1) / 2, pairs_max = c->sm_count / 2;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(2 * (pairs_needed < pairs_max ? pairs_needed : pairs_max)));
+        cfg.blockDim = dim3((unsigned)threads);
+        cfg.dynamicSmemBytes = smem_bytes;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_half, c->tmap_bias_half, pp));
+        c->launches++;
+        return 0;
+    };
     TcParams pp = p;
     pp.use_bias_mma = 0;
-    if (p.scores) return launch(tc_assign_kernel<KC, true, 3, 8, false>, TcCfg<KC, 3>::kSmemBytes, pp);
-    if (terms != 1) return launch(tc_assign_kernel<KC, false, 3, 8, false>, TcCfg<KC, 3>::kSmemBytes, pp);
+    if (p.scores) return launch(tc_assign_kernel<KC, true, 3, 8, false, 1>, TcCfg<KC, 3>::kSmemBytes, pp);
+    if (terms != 1) return launch(tc_assign_kernel<KC, false, 3, 8, false, 1>, TcCfg<KC, 3>::kSmemBytes, pp);
 #ifdef KMC_NO_BIAS_MMA      // A/B build: biases added by the epilogue (FADD per score) instead of the extra MMA step
-    return launch(tc_assign_kernel<KC, false, 1, 8, false>, TcCfg<KC, 1>::kSmemBytes, pp);
+    return launch(tc_assign_kernel<KC, false, 1, 8, false, 1>, TcCfg<KC, 1>::kSmemBytes, pp);
 #endif
     // one term: the variant that lets the MMA add the biases, and the plain one; the device runs exactly one
     pp.use_bias_mma = 1;
-    KMC_TRY(launch(tc_assign_kernel<KC, false, 1, 8, true>, TcCfg<KC, 1>::kSmemBytes, pp));
-    return launch(tc_assign_kernel<KC, false, 1, 8, false>, TcCfg<KC, 1>::kSmemBytes, pp);
+    if (c->tc_pair && p.n_mtiles >= 2)
+        KMC_TRY(launch_pair(tc_assign_kernel<KC, false, 1, 8, true, 2>, TcCfg<KC, 1, 2>::kSmemBytes, pp));
+    else
+        KMC_TRY(launch(tc_assign_kernel<KC, false, 1, 8, true, 1>, TcCfg<KC, 1>::kSmemBytes, pp));
+    return launch(tc_assign_kernel<KC, false, 1, 8, false, 1>, TcCfg<KC, 1>::kSmemBytes, pp);
 }
 
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,

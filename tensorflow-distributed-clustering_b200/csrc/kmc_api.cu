@@ -699,6 +699,9 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
                 KMC_FAIL(KMC_E_INVALID, "row chunks must be an integer in 1..%d", kMaxChunks);
             c->n_chunks = (int)value;
             return 0;
+        case KMC_PARAM_TC_PAIR:
+            c->tc_pair = value != 0.0;
+            return 0;
         case KMC_PARAM_INCREMENTAL:
             c->delta_enabled = value != 0.0;
             c->delta_valid = false;

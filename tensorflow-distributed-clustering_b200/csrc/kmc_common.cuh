@@ -123,6 +123,9 @@ struct kmc_ctx {
     alignas(64) CUtensorMap tmap_xlo;
     alignas(64) CUtensorMap tmap_c;
     alignas(64) CUtensorMap tmap_bias;
+    alignas(64) CUtensorMap tmap_c_half;      // 128-row boxes: the halves of a centroid stage a CTA pair loads
+    alignas(64) CUtensorMap tmap_bias_half;
+    bool tc_pair = true;                      // KMC_PARAM_TC_PAIR: 1-term tensor kernel on CTA pairs (cta_group::2)
     bool tmaps_ready = false;
     // pinned staging
     void* pinned[2] = {nullptr, nullptr};
