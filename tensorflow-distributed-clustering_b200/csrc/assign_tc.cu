@@ -104,7 +104,10 @@ template <int KC, int NPASS, int NCTA = 1> struct TcCfg {
     static constexpr uint32_t kAExtBytes = (NPASS == 1) ? kTcBlockM * 32 : 0;      // 128 rows x 32 B
     static constexpr uint32_t kOther = kBBytes + kAExtBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 256;
     // the points tile is double buffered whenever two copies fit next to the B ring (227 KB per CTA)
-    static constexpr int kABufs = (2 * kPlanes * KC * kTileBytesA + kOther <= 232448u) ? 2 : 1;
+    // ... and four deep for one-chunk tiles (D <= 64), whose short K sweep leaves little time per row tile to hide
+    // the load latency
+    static constexpr int kABufs = (KC == 1 && 4 * kPlanes * KC * kTileBytesA + kOther <= 232448u) ? 4
+                                : (2 * kPlanes * KC * kTileBytesA + kOther <= 232448u) ? 2 : 1;
     static constexpr uint32_t kABytes = kABufs * kPlanes * KC * kTileBytesA;
     static constexpr uint32_t kAExtOff = kABytes + kBBytes;
     static constexpr uint32_t kCnOff = kAExtOff + kAExtBytes;
@@ -313,13 +316,13 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
 
     const uint32_t bar0 = smem_base + Cfg::kBarOff;
     auto a_full = [&](int i) { return bar0 + 8u * i; };
-    auto a_empty = [&](int i) { return bar0 + 16u + 8u * i; };
-    auto b_full = [&](int i) { return bar0 + 32u + 8u * i; };
-    auto b_empty = [&](int i) { return bar0 + 32u + 8u * (Cfg::kStages + i); };
-    auto t_full = [&](int i) { return bar0 + 32u + 16u * Cfg::kStages + 8u * i; };
-    auto t_empty = [&](int i) { return bar0 + 48u + 16u * Cfg::kStages + 8u * i; };
-    static_assert(64 + 16 * Cfg::kStages + 8 <= 256, "barrier region");
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::kBarOff + 64 + 16 * Cfg::kStages);
+    auto a_empty = [&](int i) { return bar0 + 32u + 8u * i; };
+    auto b_full = [&](int i) { return bar0 + 64u + 8u * i; };
+    auto b_empty = [&](int i) { return bar0 + 64u + 8u * (Cfg::kStages + i); };
+    auto t_full = [&](int i) { return bar0 + 64u + 16u * Cfg::kStages + 8u * i; };
+    auto t_empty = [&](int i) { return bar0 + 80u + 16u * Cfg::kStages + 8u * i; };
+    static_assert(96 + 16 * Cfg::kStages + 8 <= 256 && Cfg::kABufs <= 4, "barrier region");
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::kBarOff + 96 + 16 * Cfg::kStages);
 
     // CTA pair: rank 0 (the leader) issues every MMA.  The "full" barriers of the operand stages and the "TMEM
     // buffer released" barriers are used in the leader only (both CTAs' TMA bytes and both CTAs' epilogue warps
@@ -329,7 +332,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     const bool leader = cta_rank == 0u;
     if (threadIdx.x == 0) {
         if (smem_base & 1023u) { p.stats->watchdog = 0xA11u; __trap(); }
-        for (int i = 0; i < 2; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); }
+        for (int i = 0; i < 4; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); }
         for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), EW * NCTA); }
         fence_barrier_init();
@@ -369,11 +372,17 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     const int n_units = (p.n_mtiles + NCTA - 1) / NCTA;
     const int n_my_tiles = (n_units - unit + n_units_grid - 1) / n_units_grid;
     auto tile_of = [&](int it) { return p.tile0 + (unit + it * n_units_grid) * NCTA + (int)cta_rank; };
+    // When the centroid stages of a whole K sweep fit in the ring (config 3: 256 centroids, one bias stage + one
+    // 64-column stage) they are loaded once and stay resident: no reload and no "empty" hand-off per row tile.
+    const int stages_per_tile = p.n_ntiles * ((aug ? 1 : 0) + KC * ((NPASS == 1) ? 1 : 2));
+    const bool b_resident = stages_per_tile <= Cfg::kStages;
 
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
-            uint32_t sb = 0;
+            int pslot = 0;
+            uint32_t ppar = 1u;                  // "empty" parity of the ring's current round (fresh barriers pass)
+            auto pnext = [&]() { if (++pslot == Cfg::kStages) { pslot = 0; ppar ^= 1u; } };
             // one tile load: own shared memory, bytes counted on the leader's "full" barrier (pair) or our own
             auto load_tile = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar, uint64_t policy) {
                 if (NCTA == 2) tma_load_2d_hint_pair(dst, tm, c0, c1, mapa_cluster(bar, 0u), policy);
@@ -391,32 +400,37 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         load_tile(smem_base + ((abuf * Cfg::kPlanes + pl) * KC + kc) * kTileBytesA,
                                   pl == 0 ? &tm_xhi : &tm_xlo, kc * kTcChunkK, m0, a_full(abuf), kEvictFirst);
             };
-            load_a(0);
+            constexpr int kAhead = (Cfg::kABufs > 2) ? Cfg::kABufs - 1 : 1;      // row tiles requested ahead
+            for (int j = 0; j < kAhead && j < n_my_tiles; ++j) load_a(j);
             for (int it = 0; it < n_my_tiles; ++it) {
                 for (int nt = 0; nt < p.n_ntiles; ++nt) {
+                    if (b_resident && it > 0) {
+                        if (nt == 0 && it + kAhead < n_my_tiles) load_a(it + kAhead);
+                        continue;
+                    }
                     if (aug) {      // stage of the bias plane: 256 centroids x 16 columns (8 KB of the slot)
-                        const int slot = sb % Cfg::kStages;
-                        mbar_wait<100>(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x280u + slot);
+                        const int slot = pslot;
+                        mbar_wait<100>(b_empty(slot), ppar, p.stats, 0x280u + slot);
                         if (leader) mbar_arrive_expect_tx(b_full(slot), kBiasStageBytes);
                         load_tile(smem_base + Cfg::kABytes + slot * Cfg::kStageB, &tm_bias, 0,
                                   nt * kTcBlockN + (int)cta_rank * (kTcBlockN / NCTA), b_full(slot), kEvictLast);
-                        ++sb;
+                        pnext();
                     }
                     for (int kc = 0; kc < KC; ++kc) {
 #pragma unroll
                         for (int pl = 0; pl < ((NPASS == 1) ? 1 : 2); ++pl) {
-                            const int slot = sb % Cfg::kStages;
-                            mbar_wait<100>(b_empty(slot), ((sb / Cfg::kStages) & 1u) ^ 1u, p.stats, 0x200u + slot);
+                            const int slot = pslot;
+                            mbar_wait<100>(b_empty(slot), ppar, p.stats, 0x200u + slot);
                             if (leader) mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
                             load_tile(smem_base + Cfg::kABytes + slot * Cfg::kStageB, &tm_c, kc * kTcChunkK,
                                       pl * p.K_pad + nt * kTcBlockN + (int)cta_rank * (kTcBlockN / NCTA), b_full(slot),
                                       kEvictLast);
-                            ++sb;
+                            pnext();
                         }
                     }
                     // prefetch the next row tile's points as early as its buffer can be free
-                    const int pf_after = (Cfg::kABufs == 2) ? 0 : p.n_ntiles - 1;
-                    if (nt == pf_after && it + 1 < n_my_tiles) load_a(it + 1);
+                    const int pf_after = (Cfg::kABufs >= 2) ? 0 : p.n_ntiles - 1;
+                    if (nt == pf_after && it + kAhead < n_my_tiles) load_a(it + kAhead);
                 }
             }
         }
@@ -429,12 +443,24 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             if (NCTA == 2) umma_commit_pair(bar, (uint16_t)3); else umma_commit(bar);
         };
         if (lane == 0 && leader) {
-            uint32_t sb = 0, ac = 0;
+            uint32_t ac = 0;
+            // ring position and "full" parity; resident stages: slot = position in the K sweep, and their only
+            // phase stays complete (parity 0 for ever)
+            int mslot = 0;
+            uint32_t mpar = 0u;
+            const int mwrap = b_resident ? stages_per_tile : Cfg::kStages;
+            const uint32_t mflip = b_resident ? 0u : 1u;
+            auto mnext = [&]() { if (++mslot == mwrap) { mslot = 0; mpar ^= mflip; } };
+            const uint64_t b_desc0 = umma_desc_sw128(smem_base + Cfg::kABytes);
+            const uint64_t bias_desc0 = umma_desc_sw32(smem_base + Cfg::kABytes);
+            const uint64_t ext_desc = umma_desc_sw32(smem_base + Cfg::kAExtOff);
             for (int it = 0; it < n_my_tiles; ++it) {
                 const int abuf = it % Cfg::kABufs;
                 mbar_wait<40>(a_full(abuf), ((uint32_t)it / Cfg::kABufs) & 1u, p.stats, 0x300u + abuf);
-                const uint32_t a_hi = smem_base + (abuf * Cfg::kPlanes + 0) * KC * kTileBytesA;
-                const uint32_t a_lo = smem_base + (abuf * Cfg::kPlanes + (Cfg::kPlanes - 1)) * KC * kTileBytesA;
+                // operand descriptors differ in their start-address field only (bytes >> 4, the low bits of the
+                // 64-bit word): the per-step descriptors below are base + constant, one add each in the issuing thread
+                const uint64_t a_hi = umma_desc_sw128(smem_base + (abuf * Cfg::kPlanes + 0) * KC * kTileBytesA);
+                const uint64_t a_lo = umma_desc_sw128(smem_base + (abuf * Cfg::kPlanes + (Cfg::kPlanes - 1)) * KC * kTileBytesA);
                 for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
                     const uint32_t buf = ac & 1u;
                     mbar_wait<40>(t_empty(buf), ((ac >> 1) & 1u) ^ 1u, p.stats, 0x400u + buf);
@@ -443,47 +469,44 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     const uint32_t d_tmem = tmem_base + buf * kTcBlockN;
                     uint32_t accum = 0;
                     if (aug) {      // accumulator := S*|c_k|^2 (one k-step: constants x bias pieces)
-                        const int slot = sb % Cfg::kStages;
-                        mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x580u + slot);
+                        const int slot = mslot;
+                        mbar_wait<20>(b_full(slot), mpar, p.stats, 0x580u + slot);
                         tc_fence_after_sync();
-                        mma(d_tmem, umma_desc_sw32(smem_base + Cfg::kAExtOff),
-                            umma_desc_sw32(smem_base + Cfg::kABytes + slot * Cfg::kStageB), 0);
+                        mma(d_tmem, ext_desc, bias_desc0 + (uint64_t)(slot * (int)(Cfg::kStageB >> 4)), 0);
                         accum = 1;
-                        commit(b_empty(slot));
-                        ++sb;
+                        if (!b_resident) commit(b_empty(slot));
+                        mnext();
                     }
                     for (int kc = 0; kc < KC; ++kc) {
                         // stage with the centroid hi plane: x_hi*c_hi, then x_lo*c_hi
-                        int slot = sb % Cfg::kStages;
-                        mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x500u + slot);
+                        int slot = mslot;
+                        mbar_wait<20>(b_full(slot), mpar, p.stats, 0x500u + slot);
                         tc_fence_after_sync();
-                        uint32_t b_addr = smem_base + Cfg::kABytes + slot * Cfg::kStageB;
+                        uint64_t b_desc = b_desc0 + (uint64_t)(slot * (int)(Cfg::kStageB >> 4));
+                        const uint64_t a_kc = a_hi + (uint64_t)(kc * (int)(kTileBytesA >> 4));
 #pragma unroll
                         for (int k4 = 0; k4 < 4; ++k4) {
-                            mma(d_tmem, umma_desc_sw128(a_hi + kc * kTileBytesA + k4 * 32),
-                                umma_desc_sw128(b_addr + k4 * 32), accum);
+                            mma(d_tmem, a_kc + (uint64_t)(2 * k4), b_desc + (uint64_t)(2 * k4), accum);
                             accum = 1;
                         }
                         if (NPASS == 3) {
 #pragma unroll
                             for (int k4 = 0; k4 < 4; ++k4)
-                                mma(d_tmem, umma_desc_sw128(a_lo + kc * kTileBytesA + k4 * 32),
-                                    umma_desc_sw128(b_addr + k4 * 32), 1);
+                                mma(d_tmem, a_lo + (uint64_t)(kc * (int)(kTileBytesA >> 4) + 2 * k4), b_desc + (uint64_t)(2 * k4), 1);
                         }
-                        commit(b_empty(slot));
-                        ++sb;
+                        if (!b_resident) commit(b_empty(slot));
+                        mnext();
                         if (NPASS == 1) continue;
                         // stage with the centroid lo plane: x_hi*c_lo
-                        slot = sb % Cfg::kStages;
-                        mbar_wait<20>(b_full(slot), (sb / Cfg::kStages) & 1u, p.stats, 0x600u + slot);
+                        slot = mslot;
+                        mbar_wait<20>(b_full(slot), mpar, p.stats, 0x600u + slot);
                         tc_fence_after_sync();
-                        b_addr = smem_base + Cfg::kABytes + slot * Cfg::kStageB;
+                        b_desc = b_desc0 + (uint64_t)(slot * (int)(Cfg::kStageB >> 4));
 #pragma unroll
                         for (int k4 = 0; k4 < 4; ++k4)
-                            mma(d_tmem, umma_desc_sw128(a_hi + kc * kTileBytesA + k4 * 32),
-                                umma_desc_sw128(b_addr + k4 * 32), 1);
-                        commit(b_empty(slot));
-                        ++sb;
+                            mma(d_tmem, a_kc + (uint64_t)(2 * k4), b_desc + (uint64_t)(2 * k4), 1);
+                        if (!b_resident) commit(b_empty(slot));
+                        mnext();
                     }
                     commit(t_full(buf));
                     KMC_TRACE_AT(ac, 7);
@@ -862,7 +885,9 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
 #endif
     // one term: the variant that lets the MMA add the biases, and the plain one; the device runs exactly one
     pp.use_bias_mma = 1;
-    if (c->tc_pair && p.n_mtiles >= 2)
+    // pairs pay off when a row tile meets enough MMA work to hide the cross-CTA hand-offs (config 3, one stage per
+    // row tile, is faster on single CTAs)
+    if (c->tc_pair && p.n_mtiles >= 2 && p.n_ntiles * KC >= 4)
         KMC_TRY(launch_pair(tc_assign_kernel<KC, false, 1, 8, true, 2>, TcCfg<KC, 1, 2>::kSmemBytes, pp));
     else
         KMC_TRY(launch(tc_assign_kernel<KC, false, 1, 8, true, 1>, TcCfg<KC, 1>::kSmemBytes, pp));

@@ -76,6 +76,10 @@ static int check_ready(kmc_ctx* c, bool need_centroids) {
 // Tensor path: (re)build the split centroid planes if the centroids changed outside kmc_update.
 static int ensure_planes(kmc_ctx* c, cudaStream_t s) {
     if (c->path != KMC_PATH_TC || c->planes_ready) return 0;
+    if (c->nbr_pending) {                        // a side-stream build for older centroids may still be writing
+        KMC_CUDA(cudaStreamWaitEvent(s, c->nbr_ready, 0));
+        c->nbr_pending = false;
+    }
     KMC_TRY(launch_centroid_absmax(c, s));
     KMC_TRY(launch_prep_centroids(c, s));
     if (c->off_ccdist >= 0) KMC_TRY(launch_ccdist(c, s));
@@ -86,6 +90,10 @@ static int ensure_planes(kmc_ctx* c, cudaStream_t s) {
 // exact re-decision of the rows the tensor kernel left in `worklist` (their number is in *n_work)
 static int refine_worklist(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* n_work,
                            cudaStream_t s) {
+    if (c->off_ccdist >= 0 && c->nbr_pending && s != c->side_stream) {
+        KMC_CUDA(cudaStreamWaitEvent(s, c->nbr_ready, 0));     // neighbour lists built on the side stream (kmc_update)
+        c->nbr_pending = false;
+    }
     if (c->off_ccdist >= 0) return launch_refine(c, labels, worklist, n_work, s);
     return launch_simt_assign(c, worklist, n_work, 0, labels, s);
 }
@@ -259,6 +267,7 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
             e3 = cudaEventCreateWithFlags(&c->chunk_done[i], cudaEventDisableTiming);
         if (e3 == cudaSuccess) e3 = cudaEventCreateWithFlags(&c->side_done, cudaEventDisableTiming);
         if (e3 == cudaSuccess) e3 = cudaEventCreateWithFlags(&c->side_go, cudaEventDisableTiming);
+        if (e3 == cudaSuccess) e3 = cudaEventCreateWithFlags(&c->nbr_ready, cudaEventDisableTiming);
         if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
             kmc_destroy(c);
             KMC_FAIL((int)(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)), "could not create streams / events");
@@ -285,6 +294,7 @@ void kmc_destroy(kmc_ctx* c) {
         if (e) cudaEventDestroy(e);
     if (c->side_done) cudaEventDestroy(c->side_done);
     if (c->side_go) cudaEventDestroy(c->side_go);
+    if (c->nbr_ready) cudaEventDestroy(c->nbr_ready);
     for (auto& ring : c->prof_ev)
         for (auto& e : ring)
             if (e) cudaEventDestroy(e);
@@ -545,7 +555,15 @@ int kmc_update(kmc_ctx* c, void* stream) {
     c->updated_since_acc = true;
     if (c->path == KMC_PATH_TC) {
         KMC_TRY(launch_prep_centroids(c, s));   // update_kernel refreshed c_absmax
-        if (c->off_ccdist >= 0) KMC_TRY(launch_ccdist(c, s));
+        if (c->off_ccdist >= 0) {
+            // centroid-centroid distances and sorted neighbour lists are needed by the refine only: they are
+            // built on the side stream while the next tensor pass runs (refine_worklist waits for nbr_ready)
+            KMC_CUDA(cudaEventRecord(c->side_go, s));
+            KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->side_go, 0));
+            KMC_TRY(launch_ccdist(c, c->side_stream));
+            KMC_CUDA(cudaEventRecord(c->nbr_ready, c->side_stream));
+            c->nbr_pending = true;
+        }
         c->planes_ready = true;
     }
     KMC_TRY(prof_mark(c, slot, 5, s));

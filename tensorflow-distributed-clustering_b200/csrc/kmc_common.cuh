@@ -92,6 +92,8 @@ struct kmc_ctx {
     cudaStream_t side_stream = nullptr; // refine + accumulation of chunk c run here while chunk c+1 is assigned
     cudaEvent_t chunk_done[kmc::kMaxChunks] = {};
     cudaEvent_t side_done = nullptr, side_go = nullptr;
+    cudaEvent_t nbr_ready = nullptr;    // the neighbour lists of the current centroids are complete (side stream)
+    bool nbr_pending = false;           // ... and nobody has waited for them on the caller's stream yet
     cudaEvent_t amb_event = nullptr;
     bool amb_pending = false;
     int refine_kernel = 0;              // KMC_PARAM_REFINE_KERNEL: 0 = picked on the device, 4 or 8 = fixed
