@@ -512,11 +512,13 @@ def pinned_host_copy(X_dev, N, D, K, dev):
     import torch
 
     need = N * D * 4
-    avail = psutil.virtual_memory().available
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    # every rank of the node pins its own copy at the same time: budget half of this rank's share of the host RAM
+    avail = psutil.virtual_memory().available / world * 0.5 if world > 1 else psutil.virtual_memory().available
     rows, note = N, None
-    if avail < need * 1.3 + (8 << 30):
-        rows = int(max(K, min(N, (avail - (8 << 30)) / 1.3 // (D * 4))))
-        note = f"host RAM available {avail / 1e9:.0f} GB < needed: e2e uses the first {rows} rows"
+    if avail < need * 1.3 + (8 << 30) / world:
+        rows = int(max(K, min(N, (avail - (8 << 30) / world) / 1.3 // (D * 4))))
+        note = f"host RAM budget of this rank {avail / 1e9:.0f} GB < needed: e2e uses the first {rows} rows"
     host = torch.empty((rows, D), dtype=torch.float32, pin_memory=True)
     host.copy_(X_dev[:rows])
     torch.cuda.synchronize(dev)
