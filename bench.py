@@ -292,6 +292,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-single-process", action="store_true", help="skip the one-process / all-GPUs e2e leg (N > 1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -352,8 +353,17 @@ def main():
             dist.all_reduce(shard.partials)
         shard.update()
 
-    for _ in range(args.warmup):
-        one_step()
+    def run_steps(k):
+        # one GPU: the product's own loop (kmc_iterate: no host round trip between iterations; on the small-D path
+        # one fused launch per iteration); several GPUs: accumulate / NCCL all-reduce / update per iteration
+        if world == 1:
+            if k > 0:
+                shard.iterate(k)
+        else:
+            for _ in range(k):
+                one_step()
+
+    run_steps(args.warmup)
     torch.cuda.synchronize(dev)
     shard.phase_ms()                                   # reset the phase ring after warm-up
     launches0 = shard.stats()["launches"]
@@ -365,8 +375,7 @@ def main():
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
-    for _ in range(args.steps):
-        one_step()
+    run_steps(args.steps)
     ev1.record()
     torch.cuda.synchronize(dev)
     if world > 1:
@@ -402,6 +411,12 @@ def main():
     # ---- roofline of the dominant kernel (the assignment kernel) ----
     peaks = measured_peaks()
     t_assign = phases["assign"] * 1e-3
+    fused_small = stats["path"] == "small" and world == 1
+    if fused_small:
+        # kmc_iterate on the small-D path is ONE kernel per iteration (assignment + accumulation + update), with no
+        # events inside the library: the kernel's duration is the step's
+        t_assign = ms_per_step * 1e-3
+        phases = dict(phases, assign=ms_per_step)
     flops = 2.0 * n_local * K * D
     bytes_alg = 4.0 * n_local * D
     t_tensor, t_hbm = flops / (peaks["tflops"] * 1e12), bytes_alg / (peaks["hbm_gbs"] * 1e9)
@@ -455,6 +470,11 @@ def main():
         if world == 1:
             result["e2e_pageable_f64"] = run_e2e_pageable_f64(pkg, host, C0, D, K, args.steps, dev)
         del host
+        if world > 1 and not args.no_single_process:
+            # the reference's own call shape: ONE process, GPU_names listing every device (:180-263)
+            sp = run_e2e_single_process(pkg, args, N, D, K, kind, C0, dev, world, rank)
+            if rank == 0:
+                result["e2e_single_process"] = sp
     else:
         result["e2e"] = None
 
@@ -562,6 +582,58 @@ def run_e2e(pkg, host, note, C0, D, K, steps, dev, world, n_total):
     }
     if note:
         out["note"] = note
+    return out
+
+
+def run_e2e_single_process(pkg, args, N, D, K, kind, C0, dev, world, rank):
+    """`distribuited_k_means(host_rows, K, ['/device:GPU:0', ...], C0, steps)` from ONE process driving all the
+    GPUs of the node -- the reference's call shape -- while the other ranks of this torchrun job idle: rank 0
+    regenerates the whole data set into pinned host memory (bounded by the host RAM), then times the call (shards
+    staged side by side by one host thread per GPU, first iteration under the copies, NCCL all-reduce from one
+    process, labels back)."""
+    import psutil
+    import torch
+    import torch.distributed as dist
+
+    out = None
+    torch.cuda.empty_cache()
+    torch.cuda.synchronize(dev)
+    # the idle ranks wait on the host (gloo): an NCCL barrier would park a spinning kernel on every GPU that
+    # rank 0 is about to use from its own process
+    cpu_group = dist.new_group(backend="gloo")
+    dist.barrier(group=cpu_group)
+    if rank == 0:
+        try:
+            avail = psutil.virtual_memory().available
+            rows = int(min(N, max(K * world, (avail * 0.4) // (D * 4))))
+            host = torch.empty((rows, D), dtype=torch.float32, pin_memory=True)
+            step = min(rows, 1 << 24)
+            for r0 in range(0, rows, step):
+                r1 = min(rows, r0 + step)
+                if kind == "image":
+                    blk = pkg.datagen.image_torch(2160, 3840, SEED, dev)[r0:r1]
+                else:
+                    k_true = max(2, K // 4) if args.data == "blobs4" else K
+                    blk, _ = pkg.datagen.blobs_torch(r1 - r0, D, k_true, SEED, dev, sigma=args.sigma, row0=r0,
+                                                     kind="uniform" if args.data == "uniform" else "blobs")
+                host[r0:r1].copy_(blk)
+                del blk
+            torch.cuda.synchronize(dev)
+            torch.cuda.empty_cache()
+            names = [f"/device:GPU:{i}" for i in range(world)]
+            t0 = time.perf_counter()
+            res = pkg.distribuited_k_means(host, K, names, C0, args.steps)
+            dt = time.perf_counter() - t0
+            out = {"value": rows * res["n_iter"] / dt, "unit": UNIT, "rows": rows, "gpus": world, "iterations": res["n_iter"],
+                   "seconds": dt, "initialization_time": res["initialization_time"],
+                   "computation_time": res["computation_time"], "inertia": res["inertia"],
+                   "h2d_bytes_per_step": int(rows * D * 4 / max(args.steps, 1)),
+                   "d2h_bytes_per_step": int((K * D * 4 + rows * 8) / max(args.steps, 1)),
+                   "first_iteration_streamed": res.get("first_iteration_streamed")}
+            del host, res
+        except Exception as e:                      # a leg of its own: report, do not lose the line
+            out = {"error": repr(e)}
+    dist.barrier(group=cpu_group)
     return out
 
 

@@ -331,7 +331,8 @@ def lloyd_loop(shards, n_max_iters: int, tol: float = 0.0, reduce_fn=None, first
     place -- across the list, and across processes when every rank runs this loop on its own
     shard (``reduce_fn = lambda s: torch.distributed.all_reduce(s[0].partials)``).
     ``tol > 0`` stops when the squared centre shift drops to ``tol`` (same decision on every
-    rank: the shift is computed from the reduced buffer).  ``first_accumulated``: the shards already hold
+    rank: the shift is computed from the reduced buffer, which NCCL leaves bit-identical on all ranks, in a fixed
+    summation order, see update_kernel).  ``first_accumulated``: the shards already hold
     the partial sums of the first iteration (streamed loading).  Returns (iterations, inertia, shift2).
     """
     if reduce_fn is None:
@@ -447,28 +448,45 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
 
     # ---- initialisation: H2D of every shard + centroids (:272-274) ----
     initialization_ts = time.time()
-    streamed = False
-    for s, (r0, r1) in zip(shards, ranges):
+    stream_ok = n_max_iters >= 1 and stream_first_iteration and not on_device
+    piece = batch_size if batch_size and batch_size >= (1 << 20) else None
+
+    def _load(job):
+        s, (r0, r1) = job
         s.set_centroids(init_center)
         if on_device:
             blk = data[r0:r1]
             if blk.device != s.device or blk.dtype != torch.float32 or not blk.is_contiguous():
                 blk = blk.to(device=s.device, dtype=torch.float32).contiguous()
             s.bind_points(blk)
-        elif len(shards) == 1 and n_max_iters >= 1 and stream_first_iteration:
-            # the sums of the first iteration are formed piece by piece while the rows are still arriving
-            streamed = s.stage_and_accumulate_from_host(data, r0, batch_size if batch_size and batch_size >= (1 << 20) else None)
-            if not streamed:
-                s.stage_from_host(data, r0, batch_size)
-        else:
-            s.stage_from_host(data, r0, batch_size)
+            return False
+        # the sums of the first iteration are formed piece by piece while the rows are still arriving
+        if stream_ok and s.stage_and_accumulate_from_host(data, r0, piece):
+            return True
+        s.stage_from_host(data, r0, batch_size)
+        return False
+
+    if len(shards) == 1:
+        flags = [_load((shards[0], ranges[0]))]
+    else:
+        # one host thread per GPU: the staging calls block on their own copies only (ctypes releases the GIL), so
+        # the shards load -- and run their first iteration -- side by side instead of one after the other
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=len(shards)) as pool:
+            flags = list(pool.map(_load, zip(shards, ranges)))
+    streamed = all(flags)
+    if any(flags) and not streamed:
+        for s, f in zip(shards, flags):          # mixed outcome (a shard too small to stream): plain first pass there
+            if not f:
+                s.accumulate()
+        streamed = True
     for s in shards:
         torch.cuda.synchronize(s.device)
     initialization_time = float(time.time() - initialization_ts)
 
     # ---- the Lloyd loop (:277-280) ----
     aux_ts = time.time()
-    if streamed:
+    if streamed and len(shards) == 1:
         n_iter, inertia, shift2 = lloyd_loop(shards, 1, tol, reduce_fn=lambda sh: None, first_accumulated=True)
         if n_max_iters > 1 and not (tol > 0.0 and shift2 <= tol):
             more, inertia, shift2 = shards[0].iterate(n_max_iters - 1, tol)
@@ -476,7 +494,7 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
     elif len(shards) == 1:
         n_iter, inertia, shift2 = shards[0].iterate(n_max_iters, tol)
     else:
-        n_iter, inertia, shift2 = lloyd_loop(shards, n_max_iters, tol)
+        n_iter, inertia, shift2 = lloyd_loop(shards, n_max_iters, tol, first_accumulated=streamed)
     for s in shards:
         torch.cuda.synchronize(s.device)
     computation_time = float(time.time() - aux_ts)

@@ -43,10 +43,22 @@ __device__ __forceinline__ void load_group(const float* __restrict__ x, int64_t 
     }
 }
 
-template <int D, int THREADS, bool ACCUM, bool LABELS, bool PACK>
+// FUSE (kmc_iterate on one GPU): the last CTA to flush its sums also does the centroid update (reference
+// :257-263) and clears the partial buffer of the NEXT iteration, so a whole Lloyd iteration is ONE launch and no
+// memset -- at config 1 (1M rows, 8 MB, L2-resident) launches and memsets were half of the iteration.
+struct SmallFuse {
+    float* cent_w;            // the centroids again (written by the last CTA; every CTA has read them by then)
+    float* cent_prev;
+    double* next_partials;    // cleared for the next iteration
+    DeviceStats* stats;
+    int empty_nan;
+};
+
+template <int D, int THREADS, bool ACCUM, bool LABELS, bool PACK, bool FUSE>
 __global__ void __launch_bounds__(THREADS)
 small_kernel(const float* __restrict__ x, int64_t n, const float* __restrict__ cent, int K,
-             double* __restrict__ partials, int32_t* __restrict__ labels, int vec_ok, uint32_t idx_mask) {
+             double* __restrict__ partials, int32_t* __restrict__ labels, int vec_ok, uint32_t idx_mask,
+             const SmallFuse fuse) {
     extern __shared__ __align__(16) float smem_f[];
     float* ncs = smem_f;                                  // [K*D] NEGATED centroids
     float* acc = smem_f + ((K * D + 3) & ~3);             // [K*(D+1)][THREADS]
@@ -172,11 +184,45 @@ small_kernel(const float* __restrict__ x, int64_t n, const float* __restrict__ c
         }
         double in = warp_sum((double)inertia);
         if (lane == 0 && in != 0.0) atomicAdd(partials + (int64_t)K * D + K, in);
+        if (FUSE) {
+            __shared__ unsigned int s_last;
+            __shared__ double s_shift[THREADS / 32];
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) s_last = (atomicAdd(&fuse.stats->upd_done, 1u) == gridDim.x - 1) ? 1u : 0u;
+            __syncthreads();
+            if (s_last) {
+                __threadfence();
+                const int KD = K * D;
+                double shift = 0.0;
+                for (int i = tid; i < KD; i += THREADS) {
+                    const double cnt = __ldcg(partials + KD + i / D);
+                    const float old = -ncs[i];
+                    fuse.cent_prev[i] = old;
+                    const float nw = (cnt > 0.0) ? (float)(__ldcg(partials + i) / cnt)
+                                                 : (fuse.empty_nan ? __int_as_float(0x7fc00000) : old);
+                    fuse.cent_w[i] = nw;
+                    const double d = (double)nw - (double)old;
+                    if (d == d) shift += d * d;
+                }
+                shift = warp_sum(shift);
+                if (lane == 0) s_shift[warp] = shift;
+                for (int i = tid; i < KD + K + 2; i += THREADS) fuse.next_partials[i] = 0.0;
+                __syncthreads();
+                if (tid == 0) {
+                    double t = 0.0;
+                    for (int w = 0; w < THREADS / 32; ++w) t += s_shift[w];
+                    fuse.stats->shift2 = t;
+                    fuse.stats->upd_done = 0u;
+                }
+            }
+        }
     }
 }
 
 template <int D, int THREADS>
-static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s) {
+static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s,
+                           double* partials, double* fuse_next) {
     const int K = (int)c->K;
     const size_t smem_c = (size_t)((K * D + 3) & ~3) * sizeof(float);
     const size_t smem_acc = (size_t)K * (D + 1) * THREADS * sizeof(float);
@@ -197,43 +243,55 @@ static int launch_small_dt(kmc_ctx* c, bool accumulate, int32_t* labels_out, con
     while ((1 << bits) < K) ++bits;
     const bool pack = K <= 64;
     const uint32_t idx_mask = ~((1u << bits) - 1u);
+    SmallFuse fuse = {c->centroids(), c->centroids_prev(), fuse_next, c->stats(), (c->flags & KMC_EMPTY_NAN) ? 1 : 0};
     auto launch = [&](auto kern) -> int {
         KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<(unsigned)blocks, THREADS, smem, s>>>(c->points, c->n, cent, K, c->partials(), labels_out,
-                                                     vec_ok, idx_mask);
+        kern<<<(unsigned)blocks, THREADS, smem, s>>>(c->points, c->n, cent, K, partials, labels_out,
+                                                     vec_ok, idx_mask, fuse);
         KMC_CUDA(cudaGetLastError());
         c->launches++;
         return 0;
     };
-    if (pack) {
-        if (accumulate && labels_out) return launch(small_kernel<D, THREADS, true, true, true>);
-        if (accumulate) return launch(small_kernel<D, THREADS, true, false, true>);
-        return launch(small_kernel<D, THREADS, false, true, true>);
+    if (fuse_next) {      // one launch per Lloyd iteration: accumulate + update (no labels)
+        if (pack) return launch(small_kernel<D, THREADS, true, false, true, true>);
+        return launch(small_kernel<D, THREADS, true, false, false, true>);
     }
-    if (accumulate && labels_out) return launch(small_kernel<D, THREADS, true, true, false>);
-    if (accumulate) return launch(small_kernel<D, THREADS, true, false, false>);
-    return launch(small_kernel<D, THREADS, false, true, false>);
+    if (pack) {
+        if (accumulate && labels_out) return launch(small_kernel<D, THREADS, true, true, true, false>);
+        if (accumulate) return launch(small_kernel<D, THREADS, true, false, true, false>);
+        return launch(small_kernel<D, THREADS, false, true, true, false>);
+    }
+    if (accumulate && labels_out) return launch(small_kernel<D, THREADS, true, true, false, false>);
+    if (accumulate) return launch(small_kernel<D, THREADS, true, false, false, false>);
+    return launch(small_kernel<D, THREADS, false, true, false, false>);
 }
 
 template <int D>
-static int launch_small_d(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s) {
+static int launch_small_d(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s,
+                          double* partials, double* fuse_next) {
     // 256 threads per CTA when the private accumulator columns fit twice per SM, else 128
     const size_t acc256 = (size_t)c->K * (D + 1) * 256 * sizeof(float);
-    if (!accumulate || acc256 <= 96 * 1024) return launch_small_dt<D, kSmallThreads>(c, accumulate, labels_out, cent, s);
-    return launch_small_dt<D, 128>(c, accumulate, labels_out, cent, s);
+    if (!accumulate || acc256 <= 96 * 1024) return launch_small_dt<D, kSmallThreads>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+    return launch_small_dt<D, 128>(c, accumulate, labels_out, cent, s, partials, fuse_next);
 }
 
 int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s) {
+    return launch_small_into(c, accumulate, labels_out, cent, s, c->partials(), nullptr);
+}
+
+// `partials`: where the sums go; `fuse_next` non-null: fused iteration (see SmallFuse), that buffer is cleared
+int launch_small_into(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s,
+                      double* partials, double* fuse_next) {
     if (!accumulate && !labels_out) return 0;
     switch ((int)c->D) {
-        case 1: return launch_small_d<1>(c, accumulate, labels_out, cent, s);
-        case 2: return launch_small_d<2>(c, accumulate, labels_out, cent, s);
-        case 3: return launch_small_d<3>(c, accumulate, labels_out, cent, s);
-        case 4: return launch_small_d<4>(c, accumulate, labels_out, cent, s);
-        case 5: return launch_small_d<5>(c, accumulate, labels_out, cent, s);
-        case 6: return launch_small_d<6>(c, accumulate, labels_out, cent, s);
-        case 7: return launch_small_d<7>(c, accumulate, labels_out, cent, s);
-        case 8: return launch_small_d<8>(c, accumulate, labels_out, cent, s);
+        case 1: return launch_small_d<1>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+        case 2: return launch_small_d<2>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+        case 3: return launch_small_d<3>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+        case 4: return launch_small_d<4>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+        case 5: return launch_small_d<5>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+        case 6: return launch_small_d<6>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+        case 7: return launch_small_d<7>(c, accumulate, labels_out, cent, s, partials, fuse_next);
+        case 8: return launch_small_d<8>(c, accumulate, labels_out, cent, s, partials, fuse_next);
         default: KMC_FAIL(KMC_E_UNSUPPORTED, "small path needs 1 <= D <= 8 (got %lld)", (long long)c->D);
     }
 }

@@ -600,3 +600,38 @@ def test_gpu_mirror_matches_the_numpy_oracle(pkg, cuda_device):
                                       torch.from_numpy(ref["sums"]).to(cuda_device),
                                       torch.from_numpy(ref["counts"]).to(cuda_device), ref["inertia"])
         assert cmp["label_mismatches_outside_near_ties"] == 0 and cmp["inertia_rel_err"] <= 1e-9
+
+
+@pytest.mark.parametrize("n,d,k,iters", [(50_000, 2, 8, 5), (33_333, 3, 16, 4), (10_001, 8, 40, 1), (7, 1, 3, 2)])
+def test_fused_small_path_iterate_equals_accumulate_update(n, d, k, iters, pkg, cuda_device):
+    """kmc_iterate on the small-D path runs one fused launch per iteration (the last CTA updates the centroids and
+    clears the other partial buffer); it must give what the separate kmc_accumulate / kmc_update calls give, for odd
+    and even iteration counts, and leave inertia, shift and last labels of the final iteration behind."""
+    X, _ = pkg.datagen.blobs_numpy(n, d, max(2, k // 2), seed=n)
+    C0 = X[:k].copy()
+    a = _shard(pkg, X, k, cuda_device, path="small")
+    b = _shard(pkg, X, k, cuda_device, path="small")
+    for s in (a, b):
+        s.set_centroids(C0)
+    n_iter, inertia, shift2 = a.iterate(iters)
+    for _ in range(iters):
+        b.accumulate()
+        b.update()
+    sb = b.stats()
+    assert n_iter == iters
+    assert oracle.rel_err(a.get_centroids(), b.get_centroids()) <= 1e-6
+    assert abs(inertia - sb["inertia"]) <= 1e-6 * sb["inertia"] and abs(shift2 - sb["shift2"]) <= 1e-6 * max(sb["shift2"], 1e-30)
+    pa, pb = a.partials.cpu().numpy(), b.partials.cpu().numpy()
+    assert np.array_equal(pa[k * d:k * d + k], pb[k * d:k * d + k]) and pa[k * d:k * d + k].sum() == n
+    assert np.array_equal(a.last_labels().cpu().numpy(), b.last_labels().cpu().numpy())
+    ref = oracle.run_lloyd(X, C0, iters)
+    ties = sum(int(oracle.near_tie_mask(h["d1"], h["d2"], TIE_RTOL).sum()) for h in ref["history"])
+    if ties == 0:          # (a near-tie row may legitimately go either way and moves a small cluster's centre)
+        assert oracle.rel_err(a.get_centroids(), ref["end_center"]) <= RTOL
+    assert abs(inertia - ref["history"][-1]["inertia"]) <= RTOL * ref["history"][-1]["inertia"]
+    # a second call continues from the state the first one left
+    a.iterate(1)
+    b.accumulate(); b.update()
+    assert oracle.rel_err(a.get_centroids(), b.get_centroids()) <= 1e-6
+    a.close()
+    b.close()
