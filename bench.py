@@ -444,13 +444,14 @@ def main():
                    "kernel_path": stats["path"], "seed": SEED, "parallelism": f"rows sharded over {world} GPU(s)",
                    "l2": "inputs (%.1f GB per GPU) exceed the 126 MB L2; no flush needed" % (n_local * D * 4 / 1e9)
                    if n_local * D * 4 > 4 * 126e6 else "inputs fit in L2: numbers are L2-resident",
-                   "refined_rows_last_step": stats["ambiguous"], "checks": checks,
+                   "refined_rows_last_step": stats["ambiguous"], "walk_overflow_rows_last_step": stats["walk_overflow"],
+                   "checks": checks,
                    "iterations_timed": f"Lloyd iterations {args.warmup + 1}..{args.warmup + args.steps} of one run from C0 = X[0:K] "
                                        "(the e2e leg times the whole run from iteration 1)",
                    "accumulation": "incremental: running fp64 sums updated with the rows whose label changed; a device-side "
                                    "gate takes the full pass when more than a quarter of the rows moved (every N*K distance is "
                                    "evaluated either way)" if stats["path"] != "small" else "fused into the assignment kernel",
-                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; device-side fallback to the 3-term split for chunks where >60% of the rows need the refine)"
+                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; device-side fallback to the 3-term split where the refine walks are long and >3% of a chunk is uncertified)"
                    if stats["path"] == "tc" else None},
         "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
     }

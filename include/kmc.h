@@ -14,9 +14,11 @@
  *   - All pointers named `dev_*` are device pointers valid on the ctx's device; `host_*` are
  *     host pointers.  `stream` is a `cudaStream_t` passed as `void*` (NULL = default stream).
  *     Every call is asynchronous on `stream` unless it returns values to the host.
- *   - The library allocates no large device memory: the caller provides one workspace
+ *   - The caller provides the device memory that scales with the shard: one workspace
  *     (`kmc_workspace_bytes` / `kmc_bind_workspace`) and the points buffer, and keeps both alive
- *     until `kmc_destroy`.
+ *     until `kmc_destroy`.  The library itself allocates only fixed-size staging: two pinned host buffers and,
+ *     for fp64 sources / int64 label delivery, two device buffers of 64 MB each on first use of
+ *     kmc_stage_points / kmc_labels_to_host (freed by kmc_destroy).
  *   - Return value: 0 = OK; > 0 = a cudaError_t; < 0 = a library error (KMC_E_*).  A
  *     human-readable message for the last failure on the calling thread is in kmc_last_error().
  *   - There is no CPU fallback: every entry point runs CUDA kernels or fails.
@@ -64,7 +66,9 @@ typedef struct kmc_ctx kmc_ctx;
                                   decided by the host: first pass, after a rebind) */
 #define KMC_STAT_FULL_PASS   7  /* 1: the last kmc_accumulate summed every row; 0: it updated the running sums
                                   with the changed rows only (KMC_PARAM_INCREMENTAL) */
-#define KMC_STAT_COUNT       8
+#define KMC_STAT_WALK_OVERFLOW 8 /* tensor path: refined rows of the last pass whose candidate walk hit its cap and
+                                  that the register-tiled exact kernel decided instead */
+#define KMC_STAT_COUNT       12
 
 /* Version of this ABI (major*1000 + minor). */
 int kmc_version(void);
@@ -224,8 +228,9 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
 #define KMC_PARAM_TC_GAMMA  1   /* relative error bound of the split-fp16 tensor scores used to
                                    decide which rows go to the exact refine kernel */
 #define KMC_PARAM_TC_TERMS  3   /* tensor path: MMA terms per score. 1 = hi*hi only + exact refine of every
-                                   uncertified row; 3 = fp32-accurate split; 0 (default) = start with 1 where
-                                   that pays off and fall back to 3 if too many rows need the refine */
+                                   uncertified row; 3 = fp32-accurate split; 0 (default) = start with 1 and fall
+                                   back to 3 on the device when the refine of the uncertified rows would cost more
+                                   (long candidate walks and more than 3% of the rows uncertified) */
 #define KMC_PARAM_PROFILE   2   /* non-zero: record CUDA events around each phase (see below) */
 #define KMC_PARAM_REFINE_KERNEL 4 /* exact refine of uncertified rows: 4 = warp per row (long candidate walks),
                                    8 = eight lanes per row (short walks), 0 (default) = both enqueued, the
@@ -237,6 +242,8 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
                                    it can (see kmc_accumulate); 0: every pass sums every row */
 #define KMC_PARAM_TC_PAIR   7   /* tensor path, 1-term kernel: 1 (default) = CTA pairs share every MMA (cta_group::2,
                                    M = 256: each SM stages half of every centroid tile); 0 = one CTA per MMA */
+#define KMC_PARAM_TC_TILE_N 8   /* CTA-pair kernel: centroids per accumulator tile, 256 (default, two TMEM buffers) or 128
+                                   (four buffers; measured slower at configs 4 and 5, kept for A/B runs) */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 
 /*
@@ -286,6 +293,7 @@ int kmc_kmeanspp(int device, const float* dev_points, int64_t n_rows, int64_t D,
  * larger sizes are rejected with KMC_E_NOMEM (use a kmc_ctx with a caller-provided workspace).
  *
  *   dev_points    fp32 [n_rows, D] row-major          dev_labels  int32 [n_rows], values in [0, K)
+ *                                                      (rows with other labels are left out)
  *   dev_centroids fp32 [K, D] (for the inertia)       dev_partials double [K*D + K + 2], same layout
  *                                                      as kmc_partials_ptr() (sums | counts |
  *                                                      inertia | sum |x|^2); overwritten
@@ -294,7 +302,8 @@ int kmc_kmeanspp(int device, const float* dev_points, int64_t n_rows, int64_t D,
  * runtime call), so make the first call on each device outside any stream capture.  All calls on
  * one device share the array and it keeps the previous call's contents: the function clears what
  * must start at zero, and two calls whose kernels overlap on the same GPU (different streams or
- * threads) race on it -- serialise them.
+ * threads) race on it -- serialise them.  Runs on `device` (an sm_100 GPU, checked on the first call) and puts
+ * the calling thread's current device back before returning.
  */
 int kmc_cluster_sums_noalloc(int device, const float* dev_points, const int32_t* dev_labels,
                              const float* dev_centroids, int64_t n_rows, int64_t D, int64_t K,

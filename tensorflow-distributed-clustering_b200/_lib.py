@@ -19,7 +19,8 @@ KMC_DTYPE_F32, KMC_DTYPE_F64 = 0, 1
 KMC_STAT_INERTIA, KMC_STAT_SHIFT2, KMC_STAT_AMBIGUOUS, KMC_STAT_KERNEL_PATH, KMC_STAT_LAUNCHES = 0, 1, 2, 3, 4
 KMC_STAT_X_SCALED_MAX = 5
 KMC_STAT_CHANGED, KMC_STAT_FULL_PASS = 6, 7
-KMC_STAT_COUNT = 8
+KMC_STAT_WALK_OVERFLOW = 8
+KMC_STAT_COUNT = 12
 KMC_PARAM_TC_GAMMA = 1
 KMC_PARAM_PROFILE = 2
 KMC_PARAM_TC_TERMS = 3
@@ -27,6 +28,7 @@ KMC_PARAM_REFINE_KERNEL = 4
 KMC_PARAM_CHUNKS = 5
 KMC_PARAM_INCREMENTAL = 6
 KMC_PARAM_TC_PAIR = 7
+KMC_PARAM_TC_TILE_N = 8
 KMC_PHASE_COUNT = 5
 PATH_NAMES = {KMC_PATH_SMALL: "small", KMC_PATH_SIMT: "simt", KMC_PATH_TC: "tc"}
 PATH_FLAGS = {"auto": KMC_PATH_AUTO, "small": KMC_PATH_SMALL, "simt": KMC_PATH_SIMT, "tc": KMC_PATH_TC}

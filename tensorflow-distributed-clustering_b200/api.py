@@ -244,6 +244,7 @@ class LloydShard:
             "path": L.PATH_NAMES.get(int(buf[L.KMC_STAT_KERNEL_PATH]), "?"),
             "launches": int(buf[L.KMC_STAT_LAUNCHES]),
             "changed_rows": int(buf[L.KMC_STAT_CHANGED]), "full_pass": bool(buf[L.KMC_STAT_FULL_PASS]),
+            "walk_overflow": int(buf[L.KMC_STAT_WALK_OVERFLOW]),
         }
 
     def set_param(self, param: int, value: float):

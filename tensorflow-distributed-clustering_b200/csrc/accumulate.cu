@@ -22,6 +22,7 @@
 // directly, so a cluster that is empty on this shard contributes 0, not the reference's NaN.
 #include "kmc_common.cuh"
 #include "kmc_device.cuh"
+#include <atomic>
 
 namespace kmc {
 
@@ -389,38 +390,60 @@ int launch_sorted_accumulate(kmc_ctx* c, const int32_t* labels_all, int64_t r0, 
 __global__ void __launch_bounds__(256) diff_labels_kernel(const int32_t* __restrict__ cur, const int32_t* __restrict__ prev,
                                                           int64_t n, int32_t* __restrict__ list, unsigned long long cap,
                                                           unsigned long long* __restrict__ n_chg) {
-    // a warp compares 128 consecutive rows per step: one 16-byte load per lane and label array (both label
-    // buffers are 256-byte aligned workspace regions)
+    // a warp compares 4 x 128 consecutive rows per step: four 16-byte loads per lane and label array in flight
+    // (both label buffers are 256-byte aligned workspace regions)
+    constexpr int U = 4;
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t base = warp * 128; base < n; base += nwarps * 128) {
-        const int64_t i0 = base + 4 * lane;
-        unsigned bits = 0;
-        if (i0 + 3 < n) {
-            const int4 a = *reinterpret_cast<const int4*>(cur + i0), b = *reinterpret_cast<const int4*>(prev + i0);
-            bits = (a.x != b.x ? 1u : 0u) | (a.y != b.y ? 2u : 0u) | (a.z != b.z ? 4u : 0u) | (a.w != b.w ? 8u : 0u);
-        } else {
-            for (int e = 0; e < 4; ++e)
-                if (i0 + e < n && cur[i0 + e] != prev[i0 + e]) bits |= 1u << e;
-        }
-        if (__ballot_sync(0xffffffffu, bits != 0u) == 0u) continue;
-        const int cnt = __popc(bits);
-        int incl = cnt;
+    for (int64_t base = warp * (128 * U); base < n; base += nwarps * (128 * U)) {
+        int4 a[U], b[U];
+        unsigned bits[U];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
+        for (int u = 0; u < U; ++u) {
+            const int64_t i0 = base + 128 * u + 4 * lane;
+            if (i0 + 3 < n) {
+                a[u] = __ldcs(reinterpret_cast<const int4*>(cur + i0));
+                b[u] = __ldcs(reinterpret_cast<const int4*>(prev + i0));
+            }
         }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        unsigned long long pos = 0;
-        if (lane == 0) pos = atomicAdd(n_chg, (unsigned long long)total);
-        pos = __shfl_sync(0xffffffffu, pos, 0) + (unsigned long long)(incl - cnt);
-        while (bits) {
-            const int e = __ffs(bits) - 1;
-            bits &= bits - 1u;
-            if (pos < cap) list[pos] = (int32_t)(i0 + e);
-            ++pos;
+        bool any = false;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t i0 = base + 128 * u + 4 * lane;
+            bits[u] = 0;
+            if (i0 + 3 < n) {
+                bits[u] = (a[u].x != b[u].x ? 1u : 0u) | (a[u].y != b[u].y ? 2u : 0u) | (a[u].z != b[u].z ? 4u : 0u) |
+                          (a[u].w != b[u].w ? 8u : 0u);
+            } else {
+                for (int e = 0; e < 4; ++e)
+                    if (i0 + e < n && cur[i0 + e] != prev[i0 + e]) bits[u] |= 1u << e;
+            }
+            any |= bits[u] != 0u;
+        }
+        if (__ballot_sync(0xffffffffu, any) == 0u) continue;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (__ballot_sync(0xffffffffu, bits[u] != 0u) == 0u) continue;
+            const int64_t i0 = base + 128 * u + 4 * lane;
+            unsigned w = bits[u];
+            const int cnt = __popc(w);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            unsigned long long pos = 0;
+            if (lane == 0) pos = atomicAdd(n_chg, (unsigned long long)total);
+            pos = __shfl_sync(0xffffffffu, pos, 0) + (unsigned long long)(incl - cnt);
+            while (w) {
+                const int e = __ffs(w) - 1;
+                w &= w - 1u;
+                if (pos < cap) list[pos] = (int32_t)(i0 + e);
+                ++pos;
+            }
         }
     }
 }
@@ -554,20 +577,33 @@ struct NoAllocScratch {
 // a kernel could dereference; the kernels get the device address looked up once per device.
 static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
 
-static NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+// Per device: the address of the scratch array and the SM count, published together.  Two host threads may make
+// the first call on a device at the same time: the pointer is stored last, with release ordering, and read with
+// acquire ordering, so a thread that sees it also sees the SM count (both threads would store the same values).
+static std::atomic<NoAllocScratch*> g_noalloc_ptr[kNoAllocMaxDevices];
 static int g_noalloc_sms[kNoAllocMaxDevices] = {};
 
-// First call on a device: resolve the device address of the scratch array, with that device current.
+// First call on a device: check that it is an sm_100 GPU (this library holds no other code) and resolve the
+// device address of the scratch array, with that device current.
 static int noalloc_setup(int device) {
-    if (g_noalloc_ptr[device]) return 0;
+    if (g_noalloc_ptr[device].load(std::memory_order_acquire)) return 0;
+    int major = 0, sms = 0;
+    KMC_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    if (major != 10)
+        KMC_FAIL(KMC_E_DEVICE, "device %d is sm_%dx; this library contains sm_100a code only (no fallback)", device, major);
     void* ptr = nullptr;
     KMC_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
-    int sms = 0;
     KMC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
     g_noalloc_sms[device] = sms;
-    g_noalloc_ptr[device] = static_cast<NoAllocScratch*>(ptr);
+    g_noalloc_ptr[device].store(static_cast<NoAllocScratch*>(ptr), std::memory_order_release);
     return 0;
 }
+
+// the calling thread's current device is put back when the entry point returns
+struct DeviceRestore {
+    int prev = -1;
+    ~DeviceRestore() { if (prev >= 0) cudaSetDevice(prev); }
+};
 
 }  // namespace kmc
 
@@ -587,9 +623,11 @@ extern "C" int kmc_cluster_sums_noalloc(int device, const float* dev_points, con
     if (K * D >= ((int64_t)1 << 31)) KMC_FAIL(KMC_E_INVALID, "K*D too large");
     if (!dev_partials || (n_rows > 0 && (!dev_points || !dev_labels || !dev_centroids)))
         KMC_FAIL(KMC_E_INVALID, "null argument");
+    DeviceRestore restore;
+    if (cudaGetDevice(&restore.prev) != cudaSuccess) restore.prev = -1;
     KMC_CUDA(cudaSetDevice(device));
     KMC_TRY(noalloc_setup(device));
-    NoAllocScratch* sc = g_noalloc_ptr[device];
+    NoAllocScratch* sc = g_noalloc_ptr[device].load(std::memory_order_acquire);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int Ki = (int)K, Di = (int)D;
 

@@ -16,7 +16,7 @@ constexpr int kSimtBM = 64, kSimtBN = 64, kSimtBK = 16, kSimtThreads = 256, kSim
 __global__ void __launch_bounds__(kSimtThreads)
 simt_assign_kernel(const float* __restrict__ x, int64_t n_rows_total, int D, const float* __restrict__ cent,
                    int K, const int32_t* __restrict__ worklist, const unsigned long long* __restrict__ n_work_dev,
-                   int64_t n_work_host, int32_t* __restrict__ labels) {
+                   int64_t n_work_host, int32_t* __restrict__ labels, unsigned long long* __restrict__ over_stat) {
     __shared__ __align__(16) float Xs[kSimtBK][kSimtBM + kSimtPad];
     __shared__ __align__(16) float Cs[kSimtBK][kSimtBN + kSimtPad];
     __shared__ int64_t rowidx[kSimtBM];
@@ -25,6 +25,7 @@ simt_assign_kernel(const float* __restrict__ x, int64_t n_rows_total, int D, con
     const int tx = tid & 15, ty = tid >> 4;
     int64_t n_work = n_work_dev ? (int64_t)(*n_work_dev) : n_work_host;
     if (n_work > n_rows_total) n_work = n_rows_total;
+    if (over_stat && blockIdx.x == 0 && tid == 0 && n_work > 0) atomicAdd(over_stat, (unsigned long long)n_work);
     const int64_t n_tiles = (n_work + kSimtBM - 1) / kSimtBM;
     const int lrow = tid >> 2;            // 0..63: row (or centroid) this thread stages
     const int lcol = (tid & 3) * 4;       // 0,4,8,12: first of 4 staged columns
@@ -108,7 +109,7 @@ simt_assign_kernel(const float* __restrict__ x, int64_t n_rows_total, int D, con
 }
 
 int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long long* n_work_dev,
-                       int64_t n_work_host, int32_t* labels_out, cudaStream_t s) {
+                       int64_t n_work_host, int32_t* labels_out, cudaStream_t s, unsigned long long* over_stat) {
     int64_t blocks;
     if (n_work_dev) {
         blocks = (int64_t)c->sm_count * 4;
@@ -120,7 +121,7 @@ int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long 
     if (blocks < 1) return 0;
     simt_assign_kernel<<<(unsigned)blocks, kSimtThreads, 0, s>>>(c->points, c->n, (int)c->D, c->centroids(),
                                                                  (int)c->K, worklist, n_work_dev, n_work_host,
-                                                                 labels_out);
+                                                                 labels_out, over_stat);
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;

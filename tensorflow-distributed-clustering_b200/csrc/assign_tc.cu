@@ -66,7 +66,8 @@ struct TcParams {
     int n_mtiles, n_ntiles;   // row tiles of this launch (starting at tile0), centroid tiles
     int tile0;
     unsigned long long* amb_counter;
-    const unsigned int* gate_flag;   // null, or: run only if *gate_flag != 0 (device-side fallback to 3 terms)
+    const unsigned int* gate_flag;   // null, or: run only if *gate_flag == gate_want (device-side precision policy)
+    unsigned int gate_want;
     const float* xnorm;
     const float* cnorm;
     DeviceStats* stats;
@@ -89,20 +90,28 @@ struct TcParams {
 // NCTA = 2: a CTA pair shares every MMA (cta_group::2, M = 256): each CTA stages its own 128 rows of points and
 // HALF of every centroid stage (128 centroids x 64 columns, 16 KB), so an SM pulls half the centroid bytes
 // from L2 and its tensor core reads half the B bytes from shared memory per score.
-template <int KC, int NPASS, int NCTA = 1> struct TcCfg {
+// BN = centroids per accumulator tile: 256 (two TMEM buffers, the default) or, for CTA pairs, 128 (FOUR buffers,
+// KMC_PARAM_TC_TILE_N).  Measured on one B200: four buffers are slower (config 4: 30.2 ms against 23.8 ms per pass,
+// config 5 slice: 95.7 against 79.1): twice as many tile steps, each with its fixed hand-off and bookkeeping cost,
+// outweigh the deeper MMA / epilogue overlap -- the 256-wide kernel already runs into the board's power cap.
+// (One CTA per MMA cannot use N = 128 at all: A + B would need 8 KB of shared-memory reads per 64-cycle MMA.)
+template <int KC, int NPASS, int NCTA = 1, int BN = kTcBlockN> struct TcCfg {
     static constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
-    static constexpr uint32_t kStageB = kStageBytesB / NCTA;          // bytes of one B stage in THIS CTA
-    static constexpr uint32_t kBiasStage = kBiasStageBytes / NCTA;
+    static constexpr int kTBufs = (int)kTmemCols / BN;                // accumulator tiles in TMEM
+    static constexpr uint32_t kStageBTotal = BN * 128;                // one stage: BN centroids x 64 columns
+    static constexpr uint32_t kBiasStageTotal = BN * kBiasCols * 2;
+    static constexpr uint32_t kStageB = kStageBTotal / NCTA;          // bytes of one B stage in THIS CTA
+    static constexpr uint32_t kBiasStage = kBiasStageTotal / NCTA;
 #ifndef KMC_TC_STAGES1
 #define KMC_TC_STAGES1 3
 #endif
-    static constexpr int kStages = (NCTA == 2) ? 6 : ((NPASS == 1) ? KMC_TC_STAGES1 : ((KC == 1) ? 4 : 3));
+    static constexpr int kStages = (NCTA == 2) ? (BN == 128 ? 12 : 6) : ((NPASS == 1) ? KMC_TC_STAGES1 : ((KC == 1) ? 4 : 3));
     static constexpr uint32_t kBBytes = kStages * kStageB;
     // 1 term: a constant 128 x 16 fp16 tile (32-byte swizzled) holding kBiasConst in its first columns; multiplied
     // with a stage of the bias plane it makes the MMA add S*|c_k|^2 to the accumulator (no FADD per score in the
     // epilogue)
     static constexpr uint32_t kAExtBytes = (NPASS == 1) ? kTcBlockM * 32 : 0;      // 128 rows x 32 B
-    static constexpr uint32_t kOther = kBBytes + kAExtBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 256;
+    static constexpr uint32_t kOther = kBBytes + kAExtBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 512;
     // the points tile is double buffered whenever two copies fit next to the B ring (227 KB per CTA)
     // ... and four deep for one-chunk tiles (D <= 64), whose short K sweep leaves little time per row tile to hide
     // the load latency
@@ -116,7 +125,7 @@ template <int KC, int NPASS, int NCTA = 1> struct TcCfg {
     // (with 1 term the merge has its own 1536 bytes behind the per-warp slices, so it needs no block barrier)
     static constexpr uint32_t kCnBytes = (NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4;
     static constexpr uint32_t kBarOff = kCnOff + kCnBytes;            // mbarriers
-    static constexpr uint32_t kSmemBytes = kBarOff + 256;
+    static constexpr uint32_t kSmemBytes = kBarOff + 512;
 };
 
 // Wait on an mbarrier phase.  The single-thread roles (producer, MMA issuer) share their scheduler
@@ -293,7 +302,7 @@ __device__ __forceinline__ void epi_chunk_part(const uint32_t (&r)[32], const fl
     for (int b = 0; b < 32 / kEpiG; b += 2) top2_pair(tb, bm[b], bm[b + 1]);
 }
 
-template <int KC, bool SCORES, int NPASS, int EW, bool AUG, int NCTA>   // EW = epilogue warps; AUG = bias through the MMA
+template <int KC, bool SCORES, int NPASS, int EW, bool AUG, int NCTA, int BN = kTcBlockN>   // EW = epilogue warps; AUG = bias through the MMA
 #ifndef KMC_TC_MAXNREG
 #define KMC_TC_MAXNREG 128
 #endif
@@ -301,10 +310,12 @@ __global__ void __maxnreg__(SCORES ? 128 : KMC_TC_MAXNREG)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_bias,
                  const TcParams p) {
-    using Cfg = TcCfg<KC, NPASS, NCTA>;
-    constexpr uint32_t kInstrDescT = (NCTA == 2) ? kInstrDescPair : kInstrDesc;
+    using Cfg = TcCfg<KC, NPASS, NCTA, BN>;
+    static_assert(BN == kTcBlockN || (BN == 128 && NCTA == 2), "128-centroid tiles exist for CTA pairs only");
+    constexpr int NB = Cfg::kTBufs;              // accumulator tiles in TMEM (2 or 4)
+    constexpr uint32_t kInstrDescT = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((NCTA * kTcBlockM) >> 4) << 24);
     static_assert(NCTA == 1 || (NPASS == 1 && AUG && !SCORES), "the CTA-pair kernel exists for the 1-term AUG variant");
-    if (p.gate_flag && *p.gate_flag == 0u) return;     // uniform for the whole grid
+    if (p.gate_flag && *p.gate_flag != p.gate_want) return;     // uniform for the whole grid
     // bias through the MMA (AUG): only with one term (shared memory for the extra tile) and while the fp16
     // pieces of the bias plane can represent every S*|c_k|^2.  That is a device-side fact, so the host launches
     // the AUG and the plain variant back to back and exactly one of them runs (uniform for the whole grid).
@@ -320,9 +331,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     auto b_full = [&](int i) { return bar0 + 64u + 8u * i; };
     auto b_empty = [&](int i) { return bar0 + 64u + 8u * (Cfg::kStages + i); };
     auto t_full = [&](int i) { return bar0 + 64u + 16u * Cfg::kStages + 8u * i; };
-    auto t_empty = [&](int i) { return bar0 + 80u + 16u * Cfg::kStages + 8u * i; };
-    static_assert(96 + 16 * Cfg::kStages + 8 <= 256 && Cfg::kABufs <= 4, "barrier region");
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::kBarOff + 96 + 16 * Cfg::kStages);
+    auto t_empty = [&](int i) { return bar0 + 96u + 16u * Cfg::kStages + 8u * i; };
+    static_assert(128 + 16 * Cfg::kStages + 8 <= 512 && Cfg::kABufs <= 4 && NB <= 4, "barrier region");
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + Cfg::kBarOff + 128 + 16 * Cfg::kStages);
 
     // CTA pair: rank 0 (the leader) issues every MMA.  The "full" barriers of the operand stages and the "TMEM
     // buffer released" barriers are used in the leader only (both CTAs' TMA bytes and both CTAs' epilogue warps
@@ -334,7 +345,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         if (smem_base & 1023u) { p.stats->watchdog = 0xA11u; __trap(); }
         for (int i = 0; i < 4; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); }
         for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), EW * NCTA); }
+        for (int i = 0; i < NB; ++i) { mbar_init(t_full(i), 1); mbar_init(t_empty(i), EW * NCTA); }
         fence_barrier_init();
     }
     if (warp == 0 && lane == 0) {
@@ -378,21 +389,21 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     const bool b_resident = stages_per_tile <= Cfg::kStages;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== TMA producer (whole warp, convergent; elect.sync inside the helpers) =====================
+        {
             int pslot = 0;
             uint32_t ppar = 1u;                  // "empty" parity of the ring's current round (fresh barriers pass)
             auto pnext = [&]() { if (++pslot == Cfg::kStages) { pslot = 0; ppar ^= 1u; } };
             // one tile load: own shared memory, bytes counted on the leader's "full" barrier (pair) or our own
             auto load_tile = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar, uint64_t policy) {
-                if (NCTA == 2) tma_load_2d_hint_pair(dst, tm, c0, c1, mapa_cluster(bar, 0u), policy);
-                else tma_load_2d_hint(dst, tm, c0, c1, bar, policy);
+                if (NCTA == 2) e_tma_load_2d_hint_pair(dst, tm, c0, c1, mapa_cluster(bar, 0u), policy);
+                else e_tma_load_2d_hint(dst, tm, c0, c1, bar, policy);
             };
             auto load_a = [&](int it) {
                 const int abuf = it % Cfg::kABufs;
                 const int m0 = tile_of(it) * kTcBlockM;
                 mbar_wait<200>(a_empty(abuf), (((uint32_t)it / Cfg::kABufs) & 1u) ^ 1u, p.stats, 0x100u + abuf);
-                if (leader) mbar_arrive_expect_tx(a_full(abuf), (uint32_t)NCTA * Cfg::kPlanes * KC * kTileBytesA);
+                if (leader) e_mbar_arrive_expect_tx(a_full(abuf), (uint32_t)NCTA * Cfg::kPlanes * KC * kTileBytesA);
 #pragma unroll
                 for (int pl = 0; pl < Cfg::kPlanes; ++pl)
 #pragma unroll
@@ -411,9 +422,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     if (aug) {      // stage of the bias plane: 256 centroids x 16 columns (8 KB of the slot)
                         const int slot = pslot;
                         mbar_wait<100>(b_empty(slot), ppar, p.stats, 0x280u + slot);
-                        if (leader) mbar_arrive_expect_tx(b_full(slot), kBiasStageBytes);
+                        if (leader) e_mbar_arrive_expect_tx(b_full(slot), Cfg::kBiasStageTotal);
                         load_tile(smem_base + Cfg::kABytes + slot * Cfg::kStageB, &tm_bias, 0,
-                                  nt * kTcBlockN + (int)cta_rank * (kTcBlockN / NCTA), b_full(slot), kEvictLast);
+                                  nt * BN + (int)cta_rank * (BN / NCTA), b_full(slot), kEvictLast);
                         pnext();
                     }
                     for (int kc = 0; kc < KC; ++kc) {
@@ -421,9 +432,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         for (int pl = 0; pl < ((NPASS == 1) ? 1 : 2); ++pl) {
                             const int slot = pslot;
                             mbar_wait<100>(b_empty(slot), ppar, p.stats, 0x200u + slot);
-                            if (leader) mbar_arrive_expect_tx(b_full(slot), kStageBytesB);
+                            if (leader) e_mbar_arrive_expect_tx(b_full(slot), Cfg::kStageBTotal);
                             load_tile(smem_base + Cfg::kABytes + slot * Cfg::kStageB, &tm_c, kc * kTcChunkK,
-                                      pl * p.K_pad + nt * kTcBlockN + (int)cta_rank * (kTcBlockN / NCTA), b_full(slot),
+                                      pl * p.K_pad + nt * BN + (int)cta_rank * (BN / NCTA), b_full(slot),
                                       kEvictLast);
                             pnext();
                         }
@@ -437,12 +448,12 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     } else if (warp == 1) {
         // ===================== MMA issuer (pair: the leader CTA only) =====================
         auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t acc) {
-            if (NCTA == 2) umma_f16_pair(d, da, db, kInstrDescT, acc); else umma_f16(d, da, db, kInstrDescT, acc);
+            if (NCTA == 2) e_umma_f16_pair(d, da, db, kInstrDescT, acc); else e_umma_f16(d, da, db, kInstrDescT, acc);
         };
         auto commit = [&](uint32_t bar) {
-            if (NCTA == 2) umma_commit_pair(bar, (uint16_t)3); else umma_commit(bar);
+            if (NCTA == 2) e_umma_commit_pair(bar, (uint16_t)3); else e_umma_commit(bar);
         };
-        if (lane == 0 && leader) {
+        if (leader) {          // the whole warp, convergent: elect.sync inside mma() / commit() picks the issuing lane
             uint32_t ac = 0;
             // ring position and "full" parity; resident stages: slot = position in the K sweep, and their only
             // phase stays complete (parity 0 for ever)
@@ -462,11 +473,11 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 const uint64_t a_hi = umma_desc_sw128(smem_base + (abuf * Cfg::kPlanes + 0) * KC * kTileBytesA);
                 const uint64_t a_lo = umma_desc_sw128(smem_base + (abuf * Cfg::kPlanes + (Cfg::kPlanes - 1)) * KC * kTileBytesA);
                 for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
-                    const uint32_t buf = ac & 1u;
-                    mbar_wait<40>(t_empty(buf), ((ac >> 1) & 1u) ^ 1u, p.stats, 0x400u + buf);
+                    const uint32_t buf = ac % (uint32_t)NB;
+                    mbar_wait<40>(t_empty(buf), ((ac / (uint32_t)NB) & 1u) ^ 1u, p.stats, 0x400u + buf);
                     KMC_TRACE_AT(ac, 6);
                     tc_fence_after_sync();
-                    const uint32_t d_tmem = tmem_base + buf * kTcBlockN;
+                    const uint32_t d_tmem = tmem_base + buf * BN;
                     uint32_t accum = 0;
                     if (aug) {      // accumulator := S*|c_k|^2 (one k-step: constants x bias pieces)
                         const int slot = mslot;
@@ -520,7 +531,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         // groups own the TMEM lane quarter (warp % 4).  Two warps per scheduler hide the TMEM-load
         // and min/max-chain latencies of each other.
         constexpr int kGroups = EW / 4;                 // column groups of the 256-column tile
-        constexpr int kCols = kTcBlockN / kGroups;      // columns scanned per warp and tile (128 or 64)
+        constexpr int kCols = BN / kGroups;             // columns scanned per warp and tile (128 or 64)
         constexpr int kEpiThreads = EW * 32;
         const int q = warp & 3;                         // TMEM lane quarter == warp_id % 4
         const int half = (warp - 4) >> 2;               // column group of this warp
@@ -534,8 +545,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         // row norms of the NEXT row tile are fetched while the current one is scanned
         auto tile_row = [&](int it) { return (int64_t)tile_of(it) * kTcBlockM + q * 32 + lane; };
         // "TMEM buffer released": the leader's barrier, also for the warps of the peer CTA
-        const uint32_t t_empty_c[2] = {(NCTA == 2) ? mapa_cluster(t_empty(0), 0u) : t_empty(0),
-                                       (NCTA == 2) ? mapa_cluster(t_empty(1), 0u) : t_empty(1)};
+        const uint32_t t_empty_c0 = (NCTA == 2) ? mapa_cluster(t_empty(0), 0u) : t_empty(0);
         float2 nn_next = make_float2(0.f, 0.f);
         if (n_my_tiles > 0 && tile_row(0) < p.n) nn_next = *reinterpret_cast<const float2*>(p.xnorm + 2 * tile_row(0));
         for (int it = 0; it < n_my_tiles; ++it) {
@@ -561,7 +571,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             Top2 tb = {INFINITY, INFINITY};
             int a_blk = 0;
             for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
-                const uint32_t buf = ac & 1u;
+                const uint32_t buf = ac % (uint32_t)NB;
                 const float* cn = cn_s;
                 if (aug) {
                     // the MMA already added the biases: nothing to stage
@@ -571,22 +581,22 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     float* cw = cn_s + (warp - 4) * kCols;
                     if (lane < kCols / 4)
                         *reinterpret_cast<float4*>(cw + 4 * lane) =
-                            *reinterpret_cast<const float4*>(p.cnorm + nt * kTcBlockN + half * kCols + 4 * lane);
+                            *reinterpret_cast<const float4*>(p.cnorm + nt * BN + half * kCols + 4 * lane);
                     __syncwarp();
                     cn = cw;
                 } else {
-                    float* cw = cn_s + buf * kTcBlockN;
-                    if (et < kTcBlockN) cw[et] = p.cnorm[nt * kTcBlockN + et];
+                    float* cw = cn_s + buf * BN;
+                    if (et < BN) cw[et] = p.cnorm[nt * BN + et];
                     asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
                     cn = cw + half * kCols;
                 }
                 if (threadIdx.x == 128) { KMC_TRACE_AT(ac, 0); KMC_TRACE_NS(ac, 1); }
-                mbar_wait<0>(t_full(buf), (ac >> 1) & 1u, p.stats, 0x700u + buf);
+                mbar_wait<0>(t_full(buf), (ac / (uint32_t)NB) & 1u, p.stats, 0x700u + buf);
                 if (threadIdx.x == 128) KMC_TRACE_AT(ac, 2);
                 tc_fence_after_sync();
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kTcBlockN + half * kCols;
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + half * kCols;
                 const float e_in = te.m1, o_in = to.m1, b_in = tb.m1;
-                const int kbase = nt * kTcBlockN + half * kCols;
+                const int kbase = nt * BN + half * kCols;
                 uint32_t ra[32], rb[32];
                 tmem_ld_32x32(taddr, ra);
 #pragma unroll
@@ -611,7 +621,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 __syncwarp();
                 if (threadIdx.x == 128) KMC_TRACE_AT(ac, 3);
                 if (lane == 0) {
-                    if (NCTA == 2 && !leader) mbar_arrive_cluster(t_empty_c[buf]); else mbar_arrive(t_empty(buf));
+                    if (NCTA == 2 && !leader) mbar_arrive_cluster(t_empty_c0 + 8u * buf); else mbar_arrive(t_empty(buf));
                 }
                 // a changed best value carries its column in the low bits
                 if (__float_as_uint(te.m1) != __float_as_uint(e_in)) a_e = kbase + (int)(__float_as_uint(te.m1) & 0x7Fu);
@@ -780,6 +790,11 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
                      kTcBlockN / 2));
     KMC_TRY(make_map(fn, &c->tmap_bias_half, c->at<void>(c->off_cbias), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN / 2,
                      kBiasCols, CU_TENSOR_MAP_SWIZZLE_32B));
+    // ... or its half of a 128-centroid stage (four accumulator tiles)
+    KMC_TRY(make_map(fn, &c->tmap_c_quarter, c->at<void>(c->off_cplanes), (uint64_t)c->D_pad, (uint64_t)(2 * c->K_pad),
+                     kTcBlockN / 4));
+    KMC_TRY(make_map(fn, &c->tmap_bias_quarter, c->at<void>(c->off_cbias), (uint64_t)kBiasCols, (uint64_t)c->K_pad,
+                     kTcBlockN / 4, kBiasCols, CU_TENSOR_MAP_SWIZZLE_32B));
     c->tmaps_ready = true;
     return 0;
 }
@@ -790,8 +805,9 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
 __global__ void __launch_bounds__(256) compact_worklist_kernel(const uint32_t* __restrict__ mask, int64_t w0, int64_t nw,
                                                                int32_t* __restrict__ worklist,
                                                                unsigned long long* __restrict__ counter,
-                                                               const unsigned int* __restrict__ gate_flag) {
-    if (gate_flag && *gate_flag == 0u) return;
+                                                               const unsigned int* __restrict__ gate_flag,
+                                                               unsigned int gate_want) {
+    if (gate_flag && *gate_flag != gate_want) return;
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -820,28 +836,61 @@ __global__ void __launch_bounds__(256) compact_worklist_kernel(const uint32_t* _
 }
 
 int launch_compact_worklist(kmc_ctx* c, int32_t* worklist, unsigned long long* amb_counter, int64_t r0, int64_t r1,
-                            const unsigned int* gate_flag, cudaStream_t s) {
+                            const unsigned int* gate_flag, unsigned int gate_want, cudaStream_t s) {
     const int64_t w0 = r0 >> 5, nw = ((r1 + 31) >> 5) - w0;
     if (nw <= 0) return 0;
     int64_t blocks = (nw + 255) / 256;
     const int64_t cap = (int64_t)c->sm_count * 8;
     blocks = blocks > cap ? cap : blocks;
     compact_worklist_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->at<uint32_t>(c->off_ambmask), w0, nw, worklist, amb_counter,
-                                                             gate_flag);
+                                                             gate_flag, gate_want);
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
 }
 
-// Device-side decision between the two precisions: if the 1-term pass over a chunk left more than 60% of
-// its rows uncertified, raise the chunk's flag and restart its worklist; the 3-term kernel launched right
-// behind (gated on the flag) then redoes the chunk.  Keeps the stream fully asynchronous.
-__global__ void tc_gate_kernel(unsigned long long* amb_counter, unsigned int* flag, unsigned long long limit) {
-    if (*amb_counter > limit) { *flag = 1u; *amb_counter = 0ull; } else { *flag = 0u; }
+// Device-side decision between the two precisions, per row chunk and pass.  What the uncertified rows of a 1-term
+// pass cost depends on their refine walks (measured at config 4, one B200, ns per row at full occupancy): a short
+// walk of clustered data (2-3 exact distances) 0.2 ns, a walk up to its cap ~1 ns, a row that overflows the cap
+// and goes to the register-tiled exact kernel 21 ns; the 3-term pass costs 0.37 ns more per row of the CHUNK than
+// the 1-term pass (61 against 24 ms per 100M rows) -- both of the last two scale with K*D.  So 1 term + refine wins at
+// any uncertified fraction while walks end early, and loses once overflowing rows exceed ~1.8% of the chunk.
+//   normal pass: the 1-term kernel has run; expected overflow = its uncertified rows x the overflow share of the
+//                previous refine (which also followed a 1-term pass).  Above 1.8% of the chunk: the 3-term kernel
+//                redoes the chunk, and the next `period` passes go straight to it (period doubles up to 16 while
+//                fallbacks recur, and restarts at 1 after a pass that stayed with 1 term).
+//   skip pass:   the 1-term kernel did not run; 3 terms.
+//   probe pass:  the first pass after a skip period keeps its 1-term result unconditionally, so that its refine
+//                measures the overflow share afresh (statistics of 3-term leftovers say nothing about 1-term rows).
+__global__ void tc_gate_kernel(DeviceStats* stats, int ch, unsigned long long rows, int prev_slot) {
+    unsigned long long* amb = &stats->n_amb[ch];
+    if (stats->tc_skip[ch] > 0u) {
+        if (--stats->tc_skip[ch] == 0u) stats->tc_probe[ch] = 1u;
+        stats->tc3_flag[ch] = 1u;
+        *amb = 0ull;
+        return;
+    }
+    if (stats->tc_probe[ch]) {
+        stats->tc_probe[ch] = 0u;
+        stats->tc3_flag[ch] = 0u;
+        return;
+    }
+    const unsigned long long refined = stats->walk[prev_slot][1], over = stats->walk[prev_slot][2];
+    const double expect_over = refined > 0ull ? (double)*amb * ((double)over / (double)refined) : 0.0;
+    unsigned int period = stats->tc_period[ch] ? stats->tc_period[ch] : 1u;
+    if (expect_over > 0.018 * (double)rows) {
+        stats->tc3_flag[ch] = 1u;
+        stats->tc_skip[ch] = period;
+        stats->tc_period[ch] = period < 16u ? 2u * period : 16u;
+        *amb = 0ull;
+    } else {
+        stats->tc3_flag[ch] = 0u;
+        stats->tc_period[ch] = 1u;
+    }
 }
 
-int launch_tc_gate(kmc_ctx* c, unsigned long long* amb_counter, unsigned int* flag, int64_t rows, cudaStream_t s) {
-    tc_gate_kernel<<<1, 1, 0, s>>>(amb_counter, flag, (unsigned long long)(0.6 * (double)rows));
+int launch_tc_gate(kmc_ctx* c, int ch, int64_t rows, cudaStream_t s) {
+    tc_gate_kernel<<<1, 1, 0, s>>>(c->stats(), ch, (unsigned long long)rows, (int)((c->refine_launches & 1u) ^ 1u));
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
@@ -872,7 +921,13 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_half, c->tmap_bias_half, pp));
+        if (c->tc_tile_n == 128) {
+            TcParams p4 = pp;
+            p4.n_ntiles = pp.n_ntiles * 2;
+            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_quarter, c->tmap_bias_quarter, p4));
+        } else {
+            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_half, c->tmap_bias_half, pp));
+        }
         c->launches++;
         return 0;
     };
@@ -887,8 +942,12 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
     pp.use_bias_mma = 1;
     // pairs pay off when a row tile meets enough MMA work to hide the cross-CTA hand-offs (config 3, one stage per
     // row tile, is faster on single CTAs)
-    if (c->tc_pair && p.n_mtiles >= 2 && p.n_ntiles * KC >= 4)
-        KMC_TRY(launch_pair(tc_assign_kernel<KC, false, 1, 8, true, 2>, TcCfg<KC, 1, 2>::kSmemBytes, pp));
+    if (c->tc_pair && p.n_mtiles >= 2 && p.n_ntiles * KC >= 4) {
+        if (c->tc_tile_n == 128)
+            KMC_TRY(launch_pair(tc_assign_kernel<KC, false, 1, 8, true, 2, 128>, TcCfg<KC, 1, 2, 128>::kSmemBytes, pp));
+        else
+            KMC_TRY(launch_pair(tc_assign_kernel<KC, false, 1, 8, true, 2, 256>, TcCfg<KC, 1, 2, 256>::kSmemBytes, pp));
+    }
     else
         KMC_TRY(launch(tc_assign_kernel<KC, false, 1, 8, true, 1>, TcCfg<KC, 1>::kSmemBytes, pp));
     return launch(tc_assign_kernel<KC, false, 1, 8, false, 1>, TcCfg<KC, 1>::kSmemBytes, pp);
@@ -896,7 +955,7 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
 
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
                      float* scores_out, int64_t r0, int64_t r1, int terms, const unsigned int* gate_flag,
-                     cudaStream_t s) {
+                     unsigned int gate_want, cudaStream_t s) {
     if (!c->tmaps_ready) KMC_FAIL(KMC_E_STATE, "tensor maps not built (bind workspace and points first)");
     if (r1 <= r0) return 0;
     if (r0 % kTcBlockM) KMC_FAIL(KMC_E_INVALID, "row chunks of the tensor kernel start at multiples of %d", kTcBlockM);
@@ -905,6 +964,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.tile0 = (int)(r0 / kTcBlockM);
     p.amb_counter = amb_counter;
     p.gate_flag = gate_flag;
+    p.gate_want = gate_want;
     p.K = (int)c->K;
     p.K_pad = (int)c->K_pad;
     p.n_mtiles = (int)((r1 - r0 + kTcBlockM - 1) / kTcBlockM);

@@ -56,6 +56,7 @@ static void layout_workspace(kmc_ctx* c) {
         c->off_cbias = take(c->K_pad * kBiasCols * 2);   // S*|c_k|^2 as fp16 pieces: one extra MMA k-step adds it
         c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
         c->off_ccdist = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;   // pruning table of the refine pass
+        if (c->K <= 8192) c->off_overflow = take(c->n * 4);            // rows whose refine walk hit its cap
         c->off_nbr = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;      // ... sorted nearest-first per centroid
         c->off_xhi = take(c->n * c->D_pad * 2);
         c->off_xlo = take(c->n * c->D_pad * 2);
@@ -95,45 +96,33 @@ static int refine_worklist(kmc_ctx* c, int32_t* labels, const int32_t* worklist,
         KMC_CUDA(cudaStreamWaitEvent(s, c->nbr_ready, 0));     // neighbour lists built on the side stream (kmc_update)
         c->nbr_pending = false;
     }
-    if (c->off_ccdist >= 0) return launch_refine(c, labels, worklist, n_work, s);
+    if (c->off_ccdist >= 0) {
+        // worklist = perm + r0 of a row chunk: the overflow list and its counter of the same chunk
+        const int64_t r0 = worklist - c->perm();
+        const int ch = (int)(n_work - c->stats()->n_amb);
+        return launch_refine(c, labels, worklist, n_work, c->at<int32_t>(c->off_overflow) + r0, &c->stats()->n_over[ch], s);
+    }
     return launch_simt_assign(c, worklist, n_work, 0, labels, s);
 }
 
-// adaptive precision, host side: once a finished pass is seen to have fallen back to 3 terms on the device
-// (more than 60% of a chunk uncertified), later passes start with 3 terms directly
-// One tensor pass over rows [r0, r1): with the adaptive policy a 1-term pass is followed by the on-device
-// gate and a gated 3-term pass, so poorly separated data cannot flood the exact refine kernel.
+// One tensor pass over rows [r0, r1) of row chunk `ch`.  Adaptive precision (KMC_PARAM_TC_TERMS = 0) is decided on
+// the device, pass by pass, with no host round trip: the 1-term kernel runs unless the chunk is in a "skip" period,
+// the gate kernel looks at what it left uncertified (tc_gate_kernel), and the 3-term kernel launched right behind
+// redoes the chunk if the gate raised its flag.  All of them are enqueued every time; the ones not needed return at
+// once.
 static int tc_pass(kmc_ctx* c, int32_t* labels, int64_t r0, int64_t r1, int ch, cudaStream_t s) {
     unsigned long long* cnt = &c->stats()->n_amb[ch];
-    KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, c->tc_terms_now, nullptr, s));
-    KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, nullptr, s));
-    if (c->tc_terms == 0 && c->tc_terms_now == 1) {
+    const bool adaptive = c->tc_terms == 0 && c->off_nbr >= 0;
+    const int first_terms = c->tc_terms ? c->tc_terms : (adaptive ? 1 : 3);
+    const unsigned int* skip = adaptive ? &c->stats()->tc_skip[ch] : nullptr;
+    KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, first_terms, skip, 0u, s));
+    KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, skip, 0u, s));
+    if (adaptive) {
         unsigned int* flag = &c->stats()->tc3_flag[ch];
-        KMC_TRY(launch_tc_gate(c, cnt, flag, r1 - r0, s));
-        KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, 3, flag, s));
-        KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, flag, s));
+        KMC_TRY(launch_tc_gate(c, ch, r1 - r0, s));
+        KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, 3, flag, 1u, s));
+        KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, flag, 1u, s));
     }
-    return 0;
-}
-
-static void tc_policy_poll(kmc_ctx* c) {
-    if (c->tc_terms != 0 || !c->amb_pending || cudaEventQuery(c->amb_event) != cudaSuccess) return;
-    c->amb_pending = false;
-    // amb_host: [kMaxChunks] refine counts, then [kMaxChunks] fallback flags (as 32-bit words)
-    const unsigned int* flags = reinterpret_cast<const unsigned int*>(c->amb_host + kMaxChunks);
-    bool fell_back = false;
-    for (int i = 0; i < kMaxChunks; ++i) fell_back |= flags[i] != 0u;
-    if (c->tc_terms_now == 1 && fell_back) c->tc_terms_now = 3;      // stop paying for the 1-term attempt
-}
-
-static int tc_policy_post(kmc_ctx* c, cudaStream_t s) {
-    if (c->tc_terms != 0 || c->amb_pending) return 0;
-    KMC_CUDA(cudaMemcpyAsync(c->amb_host, c->stats()->n_amb, sizeof(unsigned long long) * kMaxChunks,
-                             cudaMemcpyDeviceToHost, s));
-    KMC_CUDA(cudaMemcpyAsync(c->amb_host + kMaxChunks, c->stats()->tc3_flag, sizeof(unsigned int) * kMaxChunks,
-                             cudaMemcpyDeviceToHost, s));
-    KMC_CUDA(cudaEventRecord(c->amb_event, s));
-    c->amb_pending = true;
     return 0;
 }
 
@@ -157,10 +146,8 @@ static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -
         case KMC_PATH_TC:
             KMC_TRY(ensure_planes(c, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 0, s));    // after plane prep, before the tensor kernel
-            tc_policy_poll(c);
-            KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
+            KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * 2 * kMaxChunks, s));
             KMC_TRY(tc_pass(c, labels, 0, c->n, 0, s));
-            KMC_TRY(tc_policy_post(c, s));
             if (slot >= 0) KMC_TRY(prof_mark(c, slot, 1, s));
             return refine_worklist(c, labels, c->perm(), &c->stats()->n_amb[0], s);
     }
@@ -210,7 +197,7 @@ static int ensure_staging(kmc_ctx* c, int64_t bytes, bool need_dev) {
 
 extern "C" {
 
-int kmc_version(void) { return 1000; }
+int kmc_version(void) { return 2000; }
 
 const char* kmc_last_error(void) { return g_last_error.c_str(); }
 
@@ -260,9 +247,7 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
     if (path == KMC_PATH_TC) {
         // one tensor term + exact refine (fewer MMAs, less power, cheaper epilogue) whenever the refine pass
         // has its sorted neighbour lists; the choice is revisited from the refine counts
-        c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->off_nbr >= 0) ? 1 : 3);
-        cudaError_t e1 = cudaHostAlloc(reinterpret_cast<void**>(&c->amb_host), sizeof(unsigned long long) * 2 * kMaxChunks, cudaHostAllocDefault);
-        cudaError_t e2 = cudaEventCreateWithFlags(&c->amb_event, cudaEventDisableTiming);
+        cudaError_t e1 = cudaSuccess, e2 = cudaSuccess;
         cudaError_t e3 = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking);
         for (int i = 0; i < kMaxChunks && e3 == cudaSuccess; ++i)
             e3 = cudaEventCreateWithFlags(&c->chunk_done[i], cudaEventDisableTiming);
@@ -273,7 +258,6 @@ int kmc_create(kmc_ctx** out, int device, int64_t n_rows, int64_t D, int64_t K, 
             kmc_destroy(c);
             KMC_FAIL((int)(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)), "could not create streams / events");
         }
-        for (int i = 0; i < 2 * kMaxChunks; ++i) c->amb_host[i] = 0;
         c->n_chunks = 1;      // KMC_PARAM_CHUNKS > 1: the refine of row chunk c runs on the side stream under the tensor kernel of chunk c+1
     }
     *out = c;
@@ -288,8 +272,6 @@ void kmc_destroy(kmc_ctx* c) {
         if (c->pinned_free[i]) cudaEventDestroy(c->pinned_free[i]);
         if (c->dev_stage[i]) cudaFree(c->dev_stage[i]);
     }
-    if (c->amb_host) cudaFreeHost(c->amb_host);
-    if (c->amb_event) cudaEventDestroy(c->amb_event);
     if (c->side_stream) { cudaStreamSynchronize(c->side_stream); cudaStreamDestroy(c->side_stream); }
     for (auto& e : c->chunk_done)
         if (e) cudaEventDestroy(e);
@@ -376,15 +358,13 @@ int kmc_accumulate_rows(kmc_ctx* c, int64_t r0, int64_t r1, void* stream) {
     KMC_TRY(launch_absmax(c, c->points + r0 * c->D, (r1 - r0) * c->D, &c->stats()->x_absmax_bits, s));
     KMC_TRY(launch_split_points_range(c, r0, r1, !first, s));
     KMC_TRY(ensure_planes(c, s));
-    tc_policy_poll(c);
-    KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
+    KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * 2 * kMaxChunks, s));
     KMC_TRY(tc_pass(c, c->labels(), r0, r1, 0, s));
     KMC_TRY(refine_worklist(c, c->labels(), c->perm() + r0, &c->stats()->n_amb[0], s));
     KMC_TRY(launch_sorted_accumulate(c, c->labels(), r0, r1, 0, nullptr, s));
     c->stream_rows = r1;
     if (r1 == c->n) {
         c->streaming = false;
-        KMC_TRY(tc_policy_post(c, s));
         // same state as after kmc_accumulate: the sums of all pieces become the running state
         if (c->delta_enabled) {
             KMC_CUDA(cudaMemcpyAsync(c->running(), c->partials(), (size_t)kmc_partials_len(c) * 8, cudaMemcpyDeviceToDevice, s));
@@ -506,8 +486,7 @@ static int accumulate_impl(kmc_ctx* c, void* stream, bool zero) {
             // latency there, tensor pipe here)
             KMC_TRY(ensure_planes(c, s));
             KMC_TRY(prof_mark(c, slot, 0, s));
-            tc_policy_poll(c);
-            KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * kMaxChunks, s));
+            KMC_CUDA(cudaMemsetAsync(c->stats()->n_amb, 0, sizeof(unsigned long long) * 2 * kMaxChunks, s));
             KMC_CUDA(cudaEventRecord(c->side_go, s));                 // centroid planes and neighbour lists ready
             KMC_CUDA(cudaStreamWaitEvent(c->side_stream, c->side_go, 0));
             const int64_t tiles = (c->n + kTcBlockM - 1) / kTcBlockM;
@@ -524,7 +503,6 @@ static int accumulate_impl(kmc_ctx* c, void* stream, bool zero) {
             KMC_TRY(prof_mark(c, slot, 1, s));                        // end of the last tensor kernel
             KMC_CUDA(cudaEventRecord(c->side_done, c->side_stream));
             KMC_CUDA(cudaStreamWaitEvent(s, c->side_done, 0));        // phase "refine" = its exposed tail
-            KMC_TRY(tc_policy_post(c, s));
         } else {
             KMC_TRY(assign_into(c, c->labels(), s, slot));
         }
@@ -592,6 +570,9 @@ int kmc_read_stats(kmc_ctx* c, double* host_stats, void* stream) {
     host_stats[KMC_STAT_KERNEL_PATH] = (double)c->path;
     host_stats[KMC_STAT_LAUNCHES] = (double)c->launches;
     host_stats[KMC_STAT_X_SCALED_MAX] = (double)__builtin_bit_cast(float, st.x_absmax_bits) * (double)st.sigma_x;
+    unsigned long long over = 0;
+    for (int i = 0; i < kMaxChunks; ++i) over += st.n_over[i];
+    host_stats[KMC_STAT_WALK_OVERFLOW] = (double)over;
     host_stats[KMC_STAT_CHANGED] = c->last_pass_host_full ? (double)c->n : (double)st.n_changed;
     host_stats[KMC_STAT_FULL_PASS] = (c->last_pass_host_full || st.acc_full) ? 1.0 : 0.0;
     return 0;
@@ -730,7 +711,6 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
         case KMC_PARAM_TC_TERMS:
             if (value != 0.0 && value != 1.0 && value != 3.0) KMC_FAIL(KMC_E_INVALID, "tensor terms must be 0, 1 or 3");
             c->tc_terms = (int)value;
-            c->tc_terms_now = c->tc_terms ? c->tc_terms : ((c->off_nbr >= 0) ? 1 : 3);
             return 0;
         case KMC_PARAM_REFINE_KERNEL:
             if (value != 0.0 && value != 4.0 && value != 8.0) KMC_FAIL(KMC_E_INVALID, "refine kernel must be 0, 4 or 8");
@@ -740,6 +720,10 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             if (value < 1.0 || value > (double)kMaxChunks || value != (double)(int)value)
                 KMC_FAIL(KMC_E_INVALID, "row chunks must be an integer in 1..%d", kMaxChunks);
             c->n_chunks = (int)value;
+            return 0;
+        case KMC_PARAM_TC_TILE_N:
+            if (value != 128.0 && value != 256.0) KMC_FAIL(KMC_E_INVALID, "accumulator tiles hold 128 or 256 centroids");
+            c->tc_tile_n = (int)value;
             return 0;
         case KMC_PARAM_TC_PAIR:
             c->tc_pair = value != 0.0;
@@ -793,7 +777,7 @@ int kmc_debug_tc_scores(kmc_ctx* c, float* dev_scores, void* stream) {
     KMC_CUDA(cudaSetDevice(c->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     KMC_TRY(ensure_planes(c, s));
-    return launch_tc_assign(c, c->labels(), nullptr, &c->stats()->n_amb[0], dev_scores, 0, c->n, 3, nullptr, s);
+    return launch_tc_assign(c, c->labels(), nullptr, &c->stats()->n_amb[0], dev_scores, 0, c->n, 3, nullptr, 0u, s);
 }
 
 }  // extern "C"

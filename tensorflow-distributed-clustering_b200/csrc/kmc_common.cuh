@@ -52,6 +52,7 @@ struct DeviceStats {
     double inertia;        // last accumulate
     double shift2;         // last update
     unsigned long long n_amb[kMaxChunks];   // rows in the refine worklist of each row chunk (last tensor pass)
+    unsigned long long n_over[kMaxChunks];  // ... of them handed on to the tile kernel (walk cap reached); cleared with n_amb
     unsigned int x_absmax_bits;       // max |x| over the shard (fp32 bits), set at bind time
     unsigned int c_absmax_bits;       // max |c| after the last update / set_centroids
     unsigned int c_normmax_bits;      // max_k |C'_k| in scaled units (prep kernel)
@@ -60,11 +61,13 @@ struct DeviceStats {
     float sigma_c;                    // power-of-two scale of the centroid planes (x -2 folded)
     unsigned int c_lonormmax_bits;    // max_k |C' - C'_hi| (scaled units): bound for the 1-term kernel
     unsigned int cn_max_bits;         // max_k S*|c_k|^2 (fp32 bits): the bias plane is valid below 2^31
-    unsigned int tc3_flag[kMaxChunks];      // set on the device when a 1-term pass certified too few rows of a chunk
+    unsigned int tc3_flag[kMaxChunks];      // set by the gate: the 3-term kernel redoes this chunk in this pass
+    unsigned int tc_skip[kMaxChunks];       // passes for which the chunk goes straight to the 3-term kernel
+    unsigned int tc_period[kMaxChunks];     // length of the next skip period (1, 2, 4 ... 16)
+    unsigned int tc_probe[kMaxChunks];      // the next pass keeps its 1-term result whatever the statistics say
     // exact distances evaluated / rows handled by the last two refine launches (slot = launch parity): the next
     // launch reads the previous slot to pick the kernel that fits the walk lengths (see refine.cu)
-    unsigned long long walk_sum[2];
-    unsigned long long walk_rows[2];
+    unsigned long long walk[2][4];          // [slot]: distances evaluated, rows refined, rows handed to the tile kernel, -
     // incremental accumulation (accumulate.cu): rows whose label changed in the last pass, the part of them the
     // changed-row list holds (0 when the pass fell back to a full one), and that decision
     unsigned long long n_changed;
@@ -86,16 +89,12 @@ struct kmc_ctx {
     int64_t D_pad = 0, K_pad = 0;
     double tc_gamma = 0.0;
     int tc_terms = 0;                   // KMC_PARAM_TC_TERMS: 0 = adaptive, 1 or 3 = fixed
-    int tc_terms_now = 3;               // MMA terms of the next tensor pass
-    unsigned long long* amb_host = nullptr;   // pinned mirror of the refine counts of the last pass [kMaxChunks]
     int n_chunks = 1;                   // row chunks per accumulate pass (tensor path, large shards)
     cudaStream_t side_stream = nullptr; // refine + accumulation of chunk c run here while chunk c+1 is assigned
     cudaEvent_t chunk_done[kmc::kMaxChunks] = {};
     cudaEvent_t side_done = nullptr, side_go = nullptr;
     cudaEvent_t nbr_ready = nullptr;    // the neighbour lists of the current centroids are complete (side stream)
     bool nbr_pending = false;           // ... and nobody has waited for them on the caller's stream yet
-    cudaEvent_t amb_event = nullptr;
-    bool amb_pending = false;
     int refine_kernel = 0;              // KMC_PARAM_REFINE_KERNEL: 0 = picked on the device, 4 or 8 = fixed
     unsigned int refine_launches = 0;   // parity selects the walk-statistics slot of DeviceStats
     // workspace
@@ -105,7 +104,7 @@ struct kmc_ctx {
     int64_t off_cprev = 0, off_shift_slots = 0, off_partials_alt = 0;
     bool updated_since_acc = false;     // kmc_update ran after the last accumulate (centroids_prev() is current)
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_labels2 = 0, off_perm = 0,
-            off_changed = 0, off_running = 0,
+            off_changed = 0, off_running = 0, off_overflow = 0,
             off_sort = 0, sort_stride = 0, sort_cursor = 0, sort_offsets = 0, sort_segoff = 0,
             off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0, off_ambmask = 0,
             off_ccdist = -1, off_nbr = -1;
@@ -127,6 +126,9 @@ struct kmc_ctx {
     alignas(64) CUtensorMap tmap_bias;
     alignas(64) CUtensorMap tmap_c_half;      // 128-row boxes: the halves of a centroid stage a CTA pair loads
     alignas(64) CUtensorMap tmap_bias_half;
+    alignas(64) CUtensorMap tmap_c_quarter;   // 64-row boxes: a CTA's half of a 128-centroid stage
+    alignas(64) CUtensorMap tmap_bias_quarter;
+    int tc_tile_n = 256;                      // KMC_PARAM_TC_TILE_N: centroids per accumulator tile of the pair kernel
     bool tc_pair = true;                      // KMC_PARAM_TC_PAIR: 1-term tensor kernel on CTA pairs (cta_group::2)
     bool tmaps_ready = false;
     // pinned staging
@@ -177,24 +179,26 @@ int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* 
 int launch_small_into(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s,
                       double* partials, double* fuse_next);
 // assign_simt.cu
+// `over_stat` (may be null): the number of worklist rows is also added there (walk statistics of the refine)
 int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long long* n_work_dev,
-                       int64_t n_work_host, int32_t* labels_out, cudaStream_t s);
+                       int64_t n_work_host, int32_t* labels_out, cudaStream_t s,
+                       unsigned long long* over_stat = nullptr);
 // assign_tc.cu
 bool tc_path_supported(int64_t K, int64_t D);
 int tc_setup_tensor_maps(kmc_ctx* c);
 // rows [r0, r1) (r0 a multiple of 128); uncertified rows are appended to `worklist`, counted in `amb_counter`
-// `terms` = 1 or 3 MMA terms; `gate_flag` (may be null): the launch is a no-op unless *gate_flag != 0
+// `terms` = 1 or 3 MMA terms; `gate_flag` (may be null): the launch is a no-op unless *gate_flag == gate_want
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
                      float* scores_out, int64_t r0, int64_t r1, int terms, const unsigned int* gate_flag,
-                     cudaStream_t s);
+                     unsigned int gate_want, cudaStream_t s);
 // rows [r0, r1) (r0 a multiple of 32): masks of uncertified rows -> worklist, their number added to *amb_counter
 int launch_compact_worklist(kmc_ctx* c, int32_t* worklist, unsigned long long* amb_counter, int64_t r0, int64_t r1,
-                            const unsigned int* gate_flag, cudaStream_t s);
-int launch_tc_gate(kmc_ctx* c, unsigned long long* amb_counter, unsigned int* flag, int64_t rows, cudaStream_t s);
+                            const unsigned int* gate_flag, unsigned int gate_want, cudaStream_t s);
+int launch_tc_gate(kmc_ctx* c, int chunk, int64_t rows, cudaStream_t s);
 // refine.cu
 int launch_ccdist(kmc_ctx* c, cudaStream_t s);
 int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* n_work_dev,
-                  cudaStream_t s);
+                  int32_t* overflow, unsigned long long* n_over, cudaStream_t s);
 // accumulate.cu
 // sums / counts / inertia / sum |x|^2 of rows [r0, r1), ADDED to the partial buffer; `chunk` selects the sort
 // scratch; `gate` (may be null): device flag, the kernels run only if *gate == 1

@@ -221,6 +221,51 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar, uint16_t mask) {
                  ::"r"(bar), "h"(mask) : "memory");
 }
 
+// ---- warp-convergent issue of the single-thread instructions -------------------------------------------------
+// The TMA producer and the MMA issuer are whole warps in warp-uniform control flow; the one lane that issues is
+// chosen by elect.sync INSIDE the asm block.  (With `if (lane == 0)` around the role, the warp is divergent and
+// the compiler wraps every instruction that takes uniform registers -- UTCHMMA, UTCBAR, UTMALDG -- in an
+// ELECT / BRA.U.ANY loop: ~240 dependent instructions per tile step on the issuer's critical path.)
+#define KMC_ELECT_PRE "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+__device__ __forceinline__ void e_mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile(KMC_ELECT_PRE "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void e_tma_load_2d_hint(uint32_t dst_smem, const void* tmap, int c0, int c1, uint32_t bar,
+                                                   uint64_t policy) {
+    asm volatile(KMC_ELECT_PRE
+        "@q cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4}], [%2], %5;\n\t}"
+        ::"r"(dst_smem), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void e_tma_load_2d_hint_pair(uint32_t dst_smem, const void* tmap, int c0, int c1,
+                                                        uint32_t cluster_bar, uint64_t policy) {
+    asm volatile(KMC_ELECT_PRE
+        "@q cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4}], [%2], %5;\n\t}"
+        ::"r"(dst_smem), "l"(tmap), "r"(cluster_bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void e_umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                           uint32_t accumulate) {
+    asm volatile(KMC_ELECT_PRE ".reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void e_umma_f16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                uint32_t accumulate) {
+    asm volatile(KMC_ELECT_PRE ".reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void e_umma_commit(uint32_t bar) {
+    asm volatile(KMC_ELECT_PRE "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+                 ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void e_umma_commit_pair(uint32_t bar, uint16_t mask) {
+    asm volatile(KMC_ELECT_PRE
+                 "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+                 ::"r"(bar), "h"(mask) : "memory");
+}
+
 // K-major, 128-byte-swizzled shared-memory operand descriptor (rows of 128 bytes, 8-row
 // swizzle atoms 1024 bytes apart).  Field layout per the sm_100 UMMA descriptor:
 // [0,14) addr>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout (2 = SW128).

@@ -159,16 +159,22 @@ refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent
 // were long (far-from-converged centroids: hundreds of candidates inside the pruning radius) and the
 // 8-lanes-per-row kernel when they were short (converged blobs: two candidates).  Unknown (first launch) = long.
 __device__ __forceinline__ bool long_walks_expected(const DeviceStats* stats, int prev_slot) {
-    const unsigned long long r = stats->walk_rows[prev_slot], s = stats->walk_sum[prev_slot];
+    const unsigned long long r = stats->walk[prev_slot][1], s = stats->walk[prev_slot][0];
     return r == 0ull || s > 6ull * r;
 }
+
+// Candidates a refine walk evaluates before the row is handed to the tile kernel: K / 8 (between 32 and 256).  A walk
+// costs ~1.5 us of dependent loads per 4 candidates, the register-tiled kernel evaluates all K candidates of a row
+// at full FFMA rate; measured at K = 1024, D = 128 the two meet near 128 candidates.
+static int walk_cap_for(int64_t K) { return K / 8 < 32 ? 32 : (K / 8 > 256 ? 256 : (int)(K / 8)); }
 
 template <int NV>   // float4 slices per lane: D <= 32 * NV * 4 / 4 ... lane t owns float4 indices t, t+8, ...
 __global__ void __launch_bounds__(256)
 refine4_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
                const float* __restrict__ cc, const int32_t* __restrict__ nbr,
                const int32_t* __restrict__ worklist, const unsigned long long* __restrict__ n_work_dev,
-               int32_t* __restrict__ labels, DeviceStats* __restrict__ stats, int slot, int select) {
+               int32_t* __restrict__ labels, DeviceStats* __restrict__ stats, int slot, int select,
+               int32_t* __restrict__ overflow, unsigned long long* __restrict__ n_over, int kWalkCap) {
     if (select && !long_walks_expected(stats, slot ^ 1)) return;      // refine8_kernel runs this launch instead
     const int lane = threadIdx.x & 31, g = lane >> 3, t = lane & 7;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -191,7 +197,9 @@ refine4_kernel(const float* __restrict__ x, int D, const float* __restrict__ cen
         const int32_t* nbrow = nbr + (int64_t)a * K;
         float best = INFINITY, lim = INFINITY;
         int bk = 0x7fffffff;
-        for (int j0 = 0; j0 < K; j0 += 4) {
+        bool complete = false;
+        int j0 = 0;
+        for (; j0 < K; j0 += 4) {
             const int j = j0 + g;
             const float ccv = (j < K) ? ccrow[j] : INFINITY;
             const int k = (j < K) ? nbrow[j] : -1;
@@ -229,13 +237,20 @@ refine4_kernel(const float* __restrict__ x, int D, const float* __restrict__ cen
             if (d < best || (d == best && kk < bk)) { best = d; bk = kk; }
             walked += 4;
             // sorted: once an entry of this batch is outside the radius, all later ones are
-            if (__ballot_sync(0xffffffffu, !(ccv < lim)) != 0u) break;
+            if (__ballot_sync(0xffffffffu, !(ccv < lim)) != 0u) { complete = true; break; }
+            // bounded walk: a row with more than kWalkCap candidates inside its pruning radius (data without
+            // cluster structure, far-from-converged centroids) goes to the register-tiled exact kernel instead
+            if (j0 + 4 >= kWalkCap && j0 + 4 < K) break;
         }
-        if (lane == 0) labels[row] = (bk == 0x7fffffff) ? a : bk;
+        complete = complete || j0 >= K;
+        if (lane == 0) {
+            if (complete) labels[row] = (bk == 0x7fffffff) ? a : bk;
+            else overflow[atomicAdd(n_over, 1ull)] = (int32_t)row;
+        }
     }
     if (lane == 0 && rows_done) {
-        atomicAdd(&stats->walk_sum[slot], walked);
-        atomicAdd(&stats->walk_rows[slot], rows_done);
+        atomicAdd(&stats->walk[slot][0], walked);
+        atomicAdd(&stats->walk[slot][1], rows_done);
     }
 }
 
@@ -275,7 +290,8 @@ __global__ void __launch_bounds__(256)
 refine8_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
                const float* __restrict__ cc, const int32_t* __restrict__ nbr,
                const int32_t* __restrict__ worklist, const unsigned long long* __restrict__ n_work_dev,
-               int32_t* __restrict__ labels, DeviceStats* __restrict__ stats, int slot, int select) {
+               int32_t* __restrict__ labels, DeviceStats* __restrict__ stats, int slot, int select,
+               int32_t* __restrict__ overflow, unsigned long long* __restrict__ n_over, int kWalkCap) {
     if (select && long_walks_expected(stats, slot ^ 1)) return;       // refine4_kernel runs this launch instead
     const int lane = threadIdx.x & 31, g = lane >> 3, t = lane & 7;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -317,6 +333,7 @@ refine8_kernel(const float* __restrict__ x, int D, const float* __restrict__ cen
         if (c1 < lim) take(d1, k1);
         // sorted list: the first entry outside the radius ends the walk
         bool active = live && (c1 < lim) && (c2 < lim);
+        bool over = false;
         for (int j = 2; __any_sync(0xffffffffu, active); j += 4) {
             int kk[4];
             bool inside = true;
@@ -335,17 +352,21 @@ refine8_kernel(const float* __restrict__ x, int D, const float* __restrict__ cen
             for (int u = 0; u < 4; ++u) take(dd[u], kk[u]);
             if (active) walked += 4;
             active = inside;
+            if (active && j + 4 >= kWalkCap && j + 4 < K) { over = true; active = false; }     // bounded walk
         }
-        if (live && t == 0) labels[row] = (bk == 0x7fffffff) ? a : bk;
+        if (live && t == 0) {
+            if (over) overflow[atomicAdd(n_over, 1ull)] = (int32_t)row;
+            else labels[row] = (bk == 0x7fffffff) ? a : bk;
+        }
     }
     if (t == 0 && rows_done) {
-        atomicAdd(&stats->walk_sum[slot], walked);
-        atomicAdd(&stats->walk_rows[slot], rows_done);
+        atomicAdd(&stats->walk[slot][0], walked);
+        atomicAdd(&stats->walk[slot][1], rows_done);
     }
 }
 
 int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* nw,
-                  cudaStream_t s) {
+                  int32_t* overflow, unsigned long long* n_over, cudaStream_t s) {
     const int blocks = c->sm_count * 8;
     const int npl = (int)((c->D + 31) / 32);
     const float* cc = c->at<float>(c->off_ccdist);
@@ -356,16 +377,16 @@ int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const un
         // KMC_PARAM_REFINE_KERNEL = 4 | 8 pins one kernel; default: both enqueued, the device picks
         const int pin = c->refine_kernel;
         const int slot = (int)(c->refine_launches++ & 1u);
-        KMC_CUDA(cudaMemsetAsync(&c->stats()->walk_sum[slot], 0, sizeof(unsigned long long), s));
-        KMC_CUDA(cudaMemsetAsync(&c->stats()->walk_rows[slot], 0, sizeof(unsigned long long), s));
+        const int cap = walk_cap_for(c->K);
+        KMC_CUDA(cudaMemsetAsync(&c->stats()->walk[slot], 0, 4 * sizeof(unsigned long long), s));
 #define KMC_REFINE4(N)                                                                                          \
     do {                                                                                                        \
         if (pin != 8)                                                                                           \
             refine4_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, nbr,  \
-                                                     worklist, nw, labels, c->stats(), slot, pin == 0);        \
+                                                     worklist, nw, labels, c->stats(), slot, pin == 0, overflow, n_over, cap); \
         if (pin != 4)                                                                                           \
             refine8_kernel<N><<<blocks, 256, 0, s>>>(c->points, (int)c->D, c->centroids(), (int)c->K, cc, nbr,  \
-                                                     worklist, nw, labels, c->stats(), slot, pin == 0);        \
+                                                     worklist, nw, labels, c->stats(), slot, pin == 0, overflow, n_over, cap); \
         c->launches += (pin == 0);                                                                              \
     } while (0)
         if (nv <= 1) KMC_REFINE4(1);
@@ -375,7 +396,8 @@ int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const un
 #undef KMC_REFINE4
         KMC_CUDA(cudaGetLastError());
         c->launches++;
-        return 0;
+        // rows whose walk hit the cap: exact distances to all K centroids, register-tiled (none on clustered data)
+        return launch_simt_assign(c, overflow, n_over, 0, labels, s, &c->stats()->walk[slot][2]);
     }
 #define KMC_REFINE(N)                                                                                       \
     do {                                                                                                    \

@@ -11,6 +11,9 @@ checks each result against what the existing, workspace-based entry point (kmc_a
 its partial buffer for the same points, labels and centroids: counts exactly, sums and inertia within
 the 1e-4 relative tolerance the other GPU tests use.  The second call runs on a smaller problem with a
 different number of clusters, so anything left in the shared scratch by the first call would show up.
+Further cases check it directly against NumPy (bincount, float64 per-cluster sums, inertia): at exactly
+the largest sizes it accepts, with a row length that rules out 16-byte loads, and with a few labels
+outside [0, K), whose rows must simply be left out.
 This file is named so that pytest collects it last; it needs nothing from the other tests.
 """
 import ctypes
@@ -89,3 +92,37 @@ def test_noalloc_rejects_sizes_beyond_its_fixed_scratch(pkg, cuda_device):
     assert rc == -3 and b"at most 1048576 rows" in lib.kmc_last_error()
     rc = lib.kmc_cluster_sums_noalloc(0, p, p, p, 1000, 2, 4097, p, None)
     assert rc == -3 and b"at most 4096 clusters" in lib.kmc_last_error()
+
+
+def _numpy_partials(X, labels, C):
+    """Per-cluster float64 sums, counts and inertia of the rows whose label lies in [0, K)."""
+    K, D = C.shape
+    ok = (labels >= 0) & (labels < K)
+    Xo, lo = X[ok].astype(np.float64), labels[ok]
+    sums = np.zeros((K, D))
+    np.add.at(sums, lo, Xo)
+    counts = np.bincount(lo, minlength=K).astype(np.float64)
+    inertia = float(((Xo - C.astype(np.float64)[lo]) ** 2).sum())
+    return sums, counts, inertia
+
+
+@pytest.mark.parametrize("n,d,k,bad", [(1 << 20, 8, 4096, 0), (50_001, 7, 33, 0), (70_000, 16, 100, 5)])
+def test_noalloc_against_numpy_at_the_limits_and_on_odd_shapes(n, d, k, bad, pkg, cuda_device):
+    """Checked straight against NumPy: exactly 1 048 576 rows and 4096 clusters (the limits of the fixed scratch),
+    a row length of 7 floats (no 16-byte loads possible), and labels outside [0, K) (those rows are left out)."""
+    import torch
+
+    rng = np.random.default_rng(n + d)
+    X = rng.normal(0.0, 3.0, size=(n, d)).astype(np.float32)
+    C = rng.normal(0.0, 3.0, size=(k, d)).astype(np.float32)
+    labels = rng.integers(0, k, size=n).astype(np.int32)
+    if bad:
+        labels[rng.choice(n, bad, replace=False)] = np.array([-1, k, k + 7, -100, 2**30][:bad], dtype=np.int32)
+    pts, lab, cent = (torch.from_numpy(a).to(cuda_device) for a in (X, labels, C))
+    for _ in range(2):                                     # twice in a row on the shared scratch
+        got = _noalloc_partials(pkg, pts, lab, cent, cuda_device).cpu().numpy()
+        sums, counts, inertia = _numpy_partials(X, labels, C)
+        assert np.array_equal(got[k * d:k * d + k], counts) and counts.sum() == n - bad
+        assert np.max(np.abs(got[:k * d].reshape(k, d) - sums)) <= 1e-9 * max(1.0, np.max(np.abs(sums)))
+        assert abs(got[k * d + k] - inertia) <= RTOL * inertia
+    assert torch.cuda.current_device() == (cuda_device.index or 0)
