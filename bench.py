@@ -354,8 +354,7 @@ def main():
         shard.update()
 
     def run_steps(k):
-        # one GPU: the product's own loop (kmc_iterate: no host round trip between iterations; on the small-D path
-        # one fused launch per iteration); several GPUs: accumulate / NCCL all-reduce / update per iteration
+        # one GPU: the product's own loop (kmc_iterate: no host round trip between iterations); several GPUs: accumulate / NCCL all-reduce / update per iteration
         if world == 1:
             if k > 0:
                 shard.iterate(k)
@@ -413,8 +412,9 @@ def main():
     t_assign = phases["assign"] * 1e-3
     fused_small = stats["path"] == "small" and world == 1
     if fused_small:
-        # kmc_iterate on the small-D path is ONE kernel per iteration (assignment + accumulation + update), with no
-        # events inside the library: the kernel's duration is the step's
+        # kmc_iterate on the small-D path is two back-to-back launches per iteration (the streaming kernel: assignment +
+        # accumulation; a one-CTA fold + update kernel overlapped with it by programmatic dependent launch), with
+        # no events inside the library: the pair's duration is the step's
         t_assign = ms_per_step * 1e-3
         phases = dict(phases, assign=ms_per_step)
     flops = 2.0 * n_local * K * D

@@ -45,7 +45,12 @@ typedef struct kmc_ctx kmc_ctx;
 #define KMC_EMPTY_KEEP      0x0u  /* globally empty cluster keeps its previous centroid (default) */
 #define KMC_EMPTY_NAN       0x1u  /* ... becomes NaN, as the reference's 0/0 at :261 */
 #define KMC_PATH_AUTO       0x00u /* pick the kernel path from (K, D) */
-#define KMC_PATH_SMALL      0x10u /* fused FFMA assign+accumulate, centroids in shared memory */
+#define KMC_PATH_SMALL      0x10u /* fused FFMA assign+accumulate, centroids in shared memory.  For K <= 64 the
+                                     argmin compares distances whose lowest ceil(log2 K) mantissa bits carry the
+                                     centroid index: two distances closer than 2^-(23-bits) relative (<= 2^-17, inside
+                                     the 1e-5 near-tie window) resolve to the lower index, and the inertia sums the
+                                     truncated distances (low by < 2^-(23-bits) relative).  Sums, counts and the
+                                     inertia are added in a fixed order: results are bit-reproducible for a shard. */
 #define KMC_PATH_SIMT       0x20u /* exact fp32 register-tiled assign + sorted accumulate */
 #define KMC_PATH_TC         0x30u /* tcgen05/TMEM/TMA split-fp16 assign + exact refine + sorted accumulate */
 #define KMC_PATH_MASK       0xF0u

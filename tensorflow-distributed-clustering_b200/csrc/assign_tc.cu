@@ -35,13 +35,7 @@
 namespace kmc {
 
 constexpr uint32_t kTileBytesA = kTcBlockM * 128;   // 128 rows x 128 B  = 16 KB per (plane, chunk)
-constexpr uint32_t kStageBytesB = kTcBlockN * 128;  // 256 rows x 128 B  = 32 KB per stage
-constexpr uint32_t kBiasStageBytes = kTcBlockN * kBiasCols * 2;   // 256 rows x 32 B = 8 KB of a B slot
 constexpr uint32_t kTmemCols = 512;
-// kind::f16, fp16 x fp16 -> fp32, A and B K-major, M = 128, N = 256
-constexpr uint32_t kInstrDesc = (1u << 4) | ((uint32_t)(kTcBlockN >> 3) << 17) | ((uint32_t)(kTcBlockM >> 4) << 24);
-// ... and M = 256 for the MMA a CTA pair shares (cta_group::2)
-constexpr uint32_t kInstrDescPair = (1u << 4) | ((uint32_t)(kTcBlockN >> 3) << 17) | ((uint32_t)((2 * kTcBlockM) >> 4) << 24);
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
 constexpr float kPackRel = 1.6e-5f;                 // > 2^-16: relative weight of the 7 packed index bits
@@ -313,6 +307,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     using Cfg = TcCfg<KC, NPASS, NCTA, BN>;
     static_assert(BN == kTcBlockN || (BN == 128 && NCTA == 2), "128-centroid tiles exist for CTA pairs only");
     constexpr int NB = Cfg::kTBufs;              // accumulator tiles in TMEM (2 or 4)
+    // kind::f16, fp16 x fp16 -> fp32, A and B K-major, N = BN, M = 128 (one CTA) or 256 (the MMA a CTA pair shares)
     constexpr uint32_t kInstrDescT = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((NCTA * kTcBlockM) >> 4) << 24);
     static_assert(NCTA == 1 || (NPASS == 1 && AUG && !SCORES), "the CTA-pair kernel exists for the 1-term AUG variant");
     if (p.gate_flag && *p.gate_flag != p.gate_want) return;     // uniform for the whole grid

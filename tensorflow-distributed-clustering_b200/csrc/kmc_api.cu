@@ -34,7 +34,8 @@ static void layout_workspace(kmc_ctx* c) {
     c->off_cprev = take(c->K * c->D * 4);
     c->off_shift_slots = take(kUpdateMaxBlocks * 8);
     c->off_partials = take((c->K * c->D + c->K + 2) * 8);
-    if (c->path == KMC_PATH_SMALL) c->off_partials_alt = take((c->K * c->D + c->K + 2) * 8);   // fused kmc_iterate
+    if (c->path == KMC_PATH_SMALL)     // per-CTA partial values of the small-D kernel: [K*(D+1)+1][CTAs]
+        c->off_small_slots = take((c->K * (c->D + 1) + 1) * small_max_ctas(c->sm_count) * 8);
     if (c->path != KMC_PATH_SMALL) {
         // counting-sort scratch, one block per row chunk: hist | cursor | offsets | segoff
         c->sort_cursor = align256(c->K * 4);
@@ -584,15 +585,11 @@ int kmc_iterate(kmc_ctx* c, int max_iters, double tol, int* n_iter_out, double* 
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     int it = 0;
     if (c->path == KMC_PATH_SMALL && c->n > 0 && max_iters > 0) {
-        // small-D path: one launch per iteration (the last CTA of the fused kernel updates the centroids and
-        // clears the other partial buffer for the next iteration)
+        // small-D path: one launch per iteration (the last CTA of the fused kernel folds the per-CTA sums into the
+        // partial buffer and updates the centroids)
         KMC_CUDA(cudaSetDevice(c->device));
-        double* buf[2] = {c->partials(), c->at<double>(c->off_partials_alt)};
-        KMC_CUDA(cudaMemsetAsync(buf[0], 0, (size_t)kmc_partials_len(c) * 8, s));
-        int cur = 0;
         for (; it < max_iters;) {
-            KMC_TRY(launch_small_into(c, true, nullptr, c->centroids(), s, buf[cur], buf[cur ^ 1]));
-            cur ^= 1;
+            KMC_TRY(launch_small_into(c, true, nullptr, c->centroids(), s, c->partials(), true));
             ++it;
             if (tol > 0.0) {
                 double shift2 = 0.0;
@@ -601,8 +598,6 @@ int kmc_iterate(kmc_ctx* c, int max_iters, double tol, int* n_iter_out, double* 
                 if (shift2 <= tol) break;
             }
         }
-        if (cur == 0)     // the last iteration accumulated into the alternate buffer
-            KMC_CUDA(cudaMemcpyAsync(buf[0], buf[1], (size_t)kmc_partials_len(c) * 8, cudaMemcpyDeviceToDevice, s));
         c->updated_since_acc = true;
         max_iters = 0;    // fall through to the common epilogue
     }

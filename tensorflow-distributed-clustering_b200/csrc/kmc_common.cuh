@@ -73,7 +73,7 @@ struct DeviceStats {
     unsigned long long n_changed;
     unsigned long long n_changed_eff;
     unsigned int acc_full;
-    unsigned int upd_done;            // CTAs of the running update_kernel that have stored their shift2 slot
+    unsigned int upd_done;            // CTAs of the running update_kernel / small_kernel that have stored their slots
 };
 
 }  // namespace kmc
@@ -101,7 +101,7 @@ struct kmc_ctx {
     char* ws = nullptr;
     int64_t ws_bytes = 0;
     int64_t need_bytes = 0;
-    int64_t off_cprev = 0, off_shift_slots = 0, off_partials_alt = 0;
+    int64_t off_cprev = 0, off_shift_slots = 0, off_small_slots = 0;
     bool updated_since_acc = false;     // kmc_update ran after the last accumulate (centroids_prev() is current)
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_labels2 = 0, off_perm = 0,
             off_changed = 0, off_running = 0, off_overflow = 0,
@@ -177,7 +177,8 @@ int launch_split_points_range(kmc_ctx* c, int64_t r0, int64_t r1, bool keep_scal
 bool small_path_supported(int64_t K, int64_t D);
 int launch_small(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s);
 int launch_small_into(kmc_ctx* c, bool accumulate, int32_t* labels_out, const float* cent, cudaStream_t s,
-                      double* partials, double* fuse_next);
+                      double* partials, bool fused);
+int64_t small_max_ctas(int sm_count);
 // assign_simt.cu
 // `over_stat` (may be null): the number of worklist rows is also added there (walk statistics of the refine)
 int launch_simt_assign(kmc_ctx* c, const int32_t* worklist, const unsigned long long* n_work_dev,

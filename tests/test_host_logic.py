@@ -137,3 +137,80 @@ def test_drop_in_script_exposes_reference_names():
     spec.loader.exec_module(mod)
     for name in ("distribuited_k_means", "run_experiments", "main", "get_available_gpus"):
         assert callable(getattr(mod, name))
+
+
+def _load_script(name):
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location(name.replace(".py", ""), os.path.join(ROOT, "scripts", name))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_cli_main_backs_off_on_out_of_memory_and_logs_a_csv_row(tmp_path):
+    """Reference :331-360: a run that does not fit is retried with twice as many batches; the CSV row is
+    appended with the timers of the run that went through."""
+    dc = _load_script("distribuitedClustering.py")
+    X = np.arange(64, dtype=np.float64).reshape(32, 2)
+    data = tmp_path / "d.npz"
+    np.savez(data, X=X, Y=np.zeros(32))
+    seen = []
+
+    def fake(batch, K, GPU_names, initial_centers, n_max_iters):
+        seen.append(len(batch))
+        if len(batch) > 8:
+            raise RuntimeError("CUDA out of memory. Tried to allocate ...")
+        assert np.array_equal(initial_centers, X[:3])            # :325 first K rows
+        return {"end_center": np.zeros((K, 2)), "setup_time": 0.5, "initialization_time": 1.0, "computation_time": 2.0}
+
+    log = tmp_path / "log.csv"
+    rc = dc.main(32, 2, 3, ["/device:GPU:0"], 4, 99, str(log), "distributedKMeans", str(data), func=fake)
+    assert rc == 0
+    assert seen == [32, 16, 8, 8, 8, 8]                          # 1 batch fails, 2 batches fail at the first, 4 batches pass
+    lines = log.read_text().strip().splitlines()
+    assert lines[0].split(",") == dc.CSV_COLUMNS
+    assert lines[1].split(",") == ["distributedKMeans", "99", "1", "3", "32", "2", "2.0", "4.0", "8.0", "4"]
+
+
+def test_cli_main_writes_the_exception_name_and_returns_the_reference_status(tmp_path):
+    """Reference :362-377: any other exception still appends a row with the exception's name in the timer
+    columns; the exit status is 1 for a ValueError and 0 otherwise."""
+    dc = _load_script("distribuitedClustering.py")
+    data = tmp_path / "d.npz"
+    np.savez(data, X=np.zeros((8, 2)), Y=np.zeros(8))
+    log = tmp_path / "log.csv"
+
+    def bad_value(*a):
+        raise ValueError("K larger than N")
+
+    def bad_other(*a):
+        raise KeyError("x")
+
+    assert dc.main(8, 2, 3, ["/device:GPU:0"], 5, 1, str(log), "distributedKMeans", str(data), func=bad_value) == 1
+    assert dc.main(8, 2, 3, ["/device:GPU:0"], 5, 1, str(log), "distributedKMeans", str(data), func=bad_other) == 0
+    assert dc.main(8, 2, 3, ["/device:GPU:0"], 5, 1, str(log), "distributedFuzzyCMeans", str(data), func=bad_other) == 0
+    rows = [l.split(",") for l in log.read_text().strip().splitlines()[1:]]
+    assert [r[6:9] for r in rows] == [["ValueError"] * 3, ["KeyError"] * 3, ["NotImplementedError"] * 3]
+    assert all(r[9] == "5" for r in rows)
+    assert dc.is_out_of_memory(MemoryError()) and not dc.is_out_of_memory(RuntimeError("illegal address"))
+
+
+def test_sweep_walks_the_grid_and_reports_return_codes(tmp_path, monkeypatch):
+    """Reference new_experiment.py:35-64: sizes x K x GPU counts, one CLI process per cell."""
+    ne = _load_script("new_experiment.py")
+    monkeypatch.chdir(tmp_path)
+    cmds = []
+
+    def runner(cmd):
+        cmds.append(cmd)
+        return len(cmds) % 2
+
+    res = ne.run_sweep([200, 100], 3, [4, 2], [1, 2], 7, "log.csv", "data.npz", profile=False, runner=runner)
+    assert len(res) == 8 and [rc for _, rc in res] == [1, 0] * 4
+    assert res[0][0] == "distributedKMeans-GPUs1-n_obs200-n_dims3-K4.log"
+    assert "--n_GPUs=2" in cmds[1] and "--K=4" in cmds[1] and "--seed=123128" in cmds[1] and "--n_max_iters=7" in cmds[1]
+    d = np.load(tmp_path / "data.npz")
+    assert d["X"].shape == (100, 3) and set(np.unique(d["Y"])) == {0, 1}       # the last size's data file
+    prof = ne.cell_command(10, 2, 3, 1, 5, 1, "l.csv", "d.npz", "ncu_logs/x.log")
+    assert prof[0] == "ncu" and "gpu__time_duration.sum" in prof
