@@ -285,8 +285,14 @@ __device__ __forceinline__ float group_sum8(float v) {
     return v;
 }
 
+// Four CTAs per SM (64 registers): the kernel waits on the gathered point rows, and throughput follows the rows in
+// flight -- 2.35 -> 1.82 ms for the 11 M refined rows of config 4 (ncu, one B200) against three CTAs at 70 registers.
+// Tried on top of that and measured at no gain (1.75-2.0 ms each): resolving worklist entry -> label -> head of the
+// neighbour list for 1024 rows at once into shared memory (two of the four dependent hops gone), evaluating the
+// three nearest candidates together (2.3x fewer instructions), requesting the next row and label a step ahead
+// (slower: spills).  What is left is the gather itself: 6.1 GB of 512-byte rows at 3.4 TB/s.
 template <int NV>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 refine8_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent, int K,
                const float* __restrict__ cc, const int32_t* __restrict__ nbr,
                const int32_t* __restrict__ worklist, const unsigned long long* __restrict__ n_work_dev,
