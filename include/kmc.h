@@ -249,6 +249,9 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
                                    M = 256: each SM stages half of every centroid tile); 0 = one CTA per MMA */
 #define KMC_PARAM_TC_TILE_N 8   /* CTA-pair kernel: centroids per accumulator tile, 256 (default, two TMEM buffers) or 128
                                    (four buffers; measured slower at configs 4 and 5, kept for A/B runs) */
+#define KMC_PARAM_DELTA_ATOMIC_ROWS 9 /* incremental accumulation: an iteration that changed at most this many labels
+                                   applies the changed rows to the running sums with fp64 atomics (one launch) instead
+                                   of the sort + segmented sum (ten); 0 = never, negative = the default (2^21 / D) */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 
 /*

@@ -727,6 +727,10 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             c->delta_enabled = value != 0.0;
             c->delta_valid = false;
             return 0;
+        case KMC_PARAM_DELTA_ATOMIC_ROWS:
+            if (value != (double)(int64_t)value) KMC_FAIL(KMC_E_INVALID, "row count must be an integer");
+            c->delta_atomic_rows = (int64_t)value;
+            return 0;
         case KMC_PARAM_PROFILE:
             c->profile = value != 0.0;
             c->prof_acc_n = c->prof_upd_n = 0;

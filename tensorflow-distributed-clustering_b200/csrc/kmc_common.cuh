@@ -73,7 +73,8 @@ struct DeviceStats {
     unsigned long long n_changed;
     unsigned long long n_changed_eff;
     unsigned int acc_full;
-    unsigned int upd_done;            // CTAs of the running update_kernel / small_kernel that have stored their slots
+    unsigned int acc_sorted;          // incremental pass: 1 = the changed rows go through the sort + segmented sum, 0 = through atomics
+    unsigned int upd_done;            // CTAs of the running update_kernel that have stored their shift2 slot
 };
 
 }  // namespace kmc
@@ -115,6 +116,7 @@ struct kmc_ctx {
     bool last_pass_host_full = true;    // the last pass was a full one by the host's decision (no running state yet)
     int lab_cur = 0;                    // which label buffer the next pass writes
     int64_t chg_cap = 0;                // rows the changed-row list holds; more changed rows -> full pass
+    int64_t delta_atomic_rows = -1;     // KMC_PARAM_DELTA_ATOMIC_ROWS: up to this many changed rows are applied with atomics (-1: default)
     bool have_centroids = false;
     bool planes_ready = false;
     bool streaming = false;             // kmc_bind_points_streamed: rows arrive in pieces (kmc_accumulate_rows)
