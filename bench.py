@@ -506,7 +506,7 @@ def parity_check(shard, X, K, D, dev, world):
     chunk = max(1 << 14, min(1 << 18, (1 << 28) // max(K, 1)))       # ~2 GB of float64 distances per chunk
     ref = gpu_mirror.lloyd_pass_f64(X, C, chunk_rows=chunk)
     out = gpu_mirror.compare_pass(ref, labels, part[:K * D].view(K, D), part[K * D:K * D + K],
-                                  float(part[K * D + K].item()))
+                                  float(part[K * D + K].item()), X=X)
     out["pass_was_incremental"] = not stats["full_pass"]
     del ref
     if world > 1:
@@ -522,7 +522,12 @@ def parity_check(shard, X, K, D, dev, world):
         # the shard keeps going: this pass must not leave different centroids on different ranks
         dist.all_reduce(shard.partials)
     shard.update()
-    out["ok"] = bool(out["label_mismatches_outside_near_ties"] == 0 and out["sums_rel_err"] <= 1e-4
+    # The result must be the exact computation under a labelling the parity rule allows: labels identical to the
+    # oracle's outside near-ties, per-cluster sums equal to the float64 sums of the rows under the product's OWN labels
+    # (1e-5: the small-D path adds up to ~100 rows per thread in fp32 before it goes to fp64), counts off by at most
+    # the near-tie rows, inertia within 1e-4.  `sums_rel_err` (against the oracle's sums) is reported next to it: it
+    # contains the rows that may differ, 2e-5 on the BASELINE.json blobs, 1e-4 on uniform data with 6e4 near-ties.
+    out["ok"] = bool(out["label_mismatches_outside_near_ties"] == 0 and out["sums_rel_err_own_labels"] <= 1e-5
                      and out["inertia_rel_err"] <= 1e-4 and out["counts_abs_diff"] <= 2 * out["near_tie_rows"])
     return out
 

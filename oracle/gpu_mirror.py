@@ -55,15 +55,32 @@ def lloyd_pass_f64(X: torch.Tensor, C: torch.Tensor, chunk_rows: int = 1 << 18):
     return {"labels": labels, "d1": d1, "d2": d2, "sums": sums, "counts": counts, "inertia": d1.sum()}
 
 
+def sums_for_labels_f64(X: torch.Tensor, labels: torch.Tensor, K: int, chunk_rows: int = 1 << 18) -> torch.Tensor:
+    """Per-cluster float64 sums of the rows of X under GIVEN labels (reference :237-248 for those labels)."""
+    sums = torch.zeros((K, X.shape[1]), dtype=torch.float64, device=X.device)
+    for r0 in range(0, X.shape[0], chunk_rows):
+        sums.index_add_(0, labels[r0:r0 + chunk_rows].to(torch.int64), X[r0:r0 + chunk_rows].to(torch.float64))
+    return sums
+
+
 def compare_pass(ref: dict, labels: torch.Tensor, sums: torch.Tensor, counts: torch.Tensor, inertia: float,
-                 tie_rtol: float = 1e-5) -> dict:
-    """The parity figures of one pass: labels outside near-ties, counts up to near-tie rows, sums and inertia."""
+                 tie_rtol: float = 1e-5, X: torch.Tensor | None = None) -> dict:
+    """The parity figures of one pass: labels outside near-ties, counts up to near-tie rows, sums and inertia.
+    `sums_rel_err` compares with the oracle's sums, which differ by the rows the parity rule lets differ (labels
+    inside near-ties); with `X` given, `sums_rel_err_own_labels` compares with the float64 sums of the SAME rows under
+    the product's own labels, i.e. it checks the accumulation alone."""
     scale = torch.maximum(ref["d1"].abs(), ref["d2"].abs())
     near = (ref["d2"] - ref["d1"]) <= tie_rtol * scale
     diff = labels.to(torch.int64) != ref["labels"]
     n_near = int(near.sum().item())
     smax = float(ref["sums"].abs().max().item())
+    extra = {}
+    if X is not None:
+        own = sums_for_labels_f64(X, labels, ref["sums"].shape[0])
+        extra["sums_rel_err_own_labels"] = float((sums.to(torch.float64) - own).abs().max().item()) / (smax if smax > 0 else 1.0)
+        del own
     return {
+        **extra,
         "rows_checked": int(labels.numel()),
         "label_mismatches_outside_near_ties": int((diff & ~near).sum().item()),
         "label_differences_inside_near_ties": int((diff & near).sum().item()),
