@@ -627,6 +627,10 @@ def run_e2e_single_process(pkg, args, N, D, K, kind, C0, dev, world, rank):
             torch.cuda.synchronize(dev)
             torch.cuda.empty_cache()
             names = [f"/device:GPU:{i}" for i in range(world)]
+            # untimed warm-up on a few rows: this process has used one GPU so far; the CUDA contexts of the others and
+            # the single-process NCCL communicator are created on first use (about a second), once per process
+            warm = min(rows, max(K * world, 1 << 18))
+            pkg.distribuited_k_means(host[:warm], K, names, C0, 2)
             t0 = time.perf_counter()
             res = pkg.distribuited_k_means(host, K, names, C0, args.steps)
             dt = time.perf_counter() - t0

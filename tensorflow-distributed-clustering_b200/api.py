@@ -508,8 +508,15 @@ def distribuited_k_means(data_batch, K, GPU_names, initial_centers=None, n_max_i
         # buffers into one ordinary array (no pinned allocation of N labels inside the call)
         parts = [s.assign() for s in shards]                 # asynchronous on every GPU
         toucher.join()
-        for s, p, (r0, r1) in zip(shards, parts, ranges):
-            s.labels_to_host(p, cluster_idx[r0:r1])
+        if len(shards) == 1:
+            shards[0].labels_to_host(parts[0], cluster_idx[ranges[0][0]:ranges[0][1]])
+        else:
+            # one host thread per GPU again: every shard's labels travel through its own pinned buffers (the C call
+            # releases the GIL), so the device-to-host copies of the shards overlap
+            from concurrent.futures import ThreadPoolExecutor
+            with ThreadPoolExecutor(max_workers=len(shards)) as pool:
+                list(pool.map(lambda job: job[0].labels_to_host(job[1], cluster_idx[job[2][0]:job[2][1]]),
+                              zip(shards, parts, ranges)))
         if n_iter >= 1:
             # `centroids` (:279, :286): the last GPU's labels of the final iteration, against the centroids
             # BEFORE its update -- not a slice of cluster_idx, which is computed after it (:282)

@@ -71,6 +71,7 @@ struct TcParams {
     float* scores;       // debug: [n, K] or nullptr
     float gamma;         // accumulate + split error of the 3-term score, relative to |X'||C'|
     float gamma1;        // accumulate error of the 1-term score
+    float gamma16;       // fp16 accumulators: (MMA instructions per tile) * 2^-10
     int use_bias_mma;    // this launch is one of the AUG / plain pair: run only if AUG matches the device-side check
     uint32_t pack_mask;  // 0xFFFFFF80, see pack_idx
     uint32_t blk_mask;   // ~(128 / kEpiG - 1): the packed block index of the partition epilogue
@@ -277,6 +278,9 @@ __device__ __forceinline__ void epi_chunk_part(const uint32_t (&r)[32], const fl
             ga[g] = fmin3(ga[g], v[g], v[16 + g]);
         }
     }
+#ifdef KMC_ABL_NO_B
+    return;
+#endif
     // partition B
     float bm[32 / kEpiG];
 #pragma unroll
@@ -296,7 +300,47 @@ __device__ __forceinline__ void epi_chunk_part(const uint32_t (&r)[32], const fl
     for (int b = 0; b < 32 / kEpiG; b += 2) top2_pair(tb, bm[b], bm[b + 1]);
 }
 
-template <int KC, bool SCORES, int NPASS, int EW, bool AUG, int NCTA, int BN = kTcBlockN>   // EW = epilogue warps; AUG = bias through the MMA
+// ---- fp16-accumulator tier (ACC16) ---------------------------------------------------------------
+// The same exact partition scheme on packed half2 registers: with fp16 accumulators a tcgen05.ld delivers two
+// scores per register and HMNMX2 (one dispatch cycle) handles both, so a score costs ~1.2 dispatch cycles
+// instead of 2.9.  Per thread and 64-column load (32 registers):
+//   A: register index mod 16, and the half -> 32 running minima (16 half2), one HMNMX2 per register;
+//   B: 16 consecutive registers = a block of 32 columns -> a 15-deep... 15-op HMNMX2 tree, the two halves merged
+//      in fp32 (the conversion is exact and leaves 13 zero mantissa bits: the 2-bit block number packs without
+//      any truncation), then the exact top-2 chain over block minima.
+// A cell and a block share exactly one column, so best / second best / column follow as in the fp32 scheme.
+constexpr int kH2Cells = 16;                        // half2 registers of partition A (32 cells)
+__device__ __forceinline__ __half2 as_h2(uint32_t v) { return *reinterpret_cast<const __half2*>(&v); }
+// min of two half2 as ONE HMNMX2 (full rate).  Through __hmin2 the compiler fuses pairs of them into the 3-input
+// VHMNMX, which the epilogue measured slower than the two instructions it replaces; the asm statement keeps them apart.
+__device__ __forceinline__ uint32_t h2min(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("min.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+
+__device__ __forceinline__ void epi_chunk_h2(const uint32_t (&r)[32], int blk0, uint32_t mask, uint32_t (&ga)[kH2Cells],
+                                             Top2& tb) {
+#pragma unroll
+    for (int j = 0; j < kH2Cells; ++j) {
+        ga[j] = h2min(ga[j], r[j]);
+        ga[j] = h2min(ga[j], r[kH2Cells + j]);
+    }
+    float bm[2];
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+        const uint32_t* w = r + b * 16;
+        const uint32_t t0 = h2min(h2min(w[0], w[1]), h2min(w[2], w[3]));
+        const uint32_t t1 = h2min(h2min(w[4], w[5]), h2min(w[6], w[7]));
+        const uint32_t t2 = h2min(h2min(w[8], w[9]), h2min(w[10], w[11]));
+        const uint32_t t3 = h2min(h2min(w[12], w[13]), h2min(w[14], w[15]));
+        const __half2 m = as_h2(h2min(h2min(t0, t1), h2min(t2, t3)));
+        bm[b] = pack_idx(fminf(__low2float(m), __high2float(m)), blk0 + b, mask);
+    }
+    top2_pair(tb, bm[0], bm[1]);
+}
+
+template <int KC, bool SCORES, int NPASS, int EW, bool AUG, int NCTA, int BN = kTcBlockN, bool ACC16 = false>   // EW = epilogue warps; AUG = bias through the MMA
 #ifndef KMC_TC_MAXNREG
 #define KMC_TC_MAXNREG 128
 #endif
@@ -308,14 +352,21 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     static_assert(BN == kTcBlockN || (BN == 128 && NCTA == 2), "128-centroid tiles exist for CTA pairs only");
     constexpr int NB = Cfg::kTBufs;              // accumulator tiles in TMEM (2 or 4)
     // kind::f16, fp16 x fp16 -> fp32, A and B K-major, N = BN, M = 128 (one CTA) or 256 (the MMA a CTA pair shares)
-    constexpr uint32_t kInstrDescT = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((NCTA * kTcBlockM) >> 4) << 24);
+    // ... accumulator (bits 4-5): 1 = fp32, 0 = fp16 (ACC16)
+#ifdef KMC_ABL_F32DESC
+    constexpr uint32_t kAccFmt = 1u;
+#else
+    constexpr uint32_t kAccFmt = ACC16 ? 0u : 1u;
+#endif
+    constexpr uint32_t kInstrDescT = (kAccFmt << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((NCTA * kTcBlockM) >> 4) << 24);
+    static_assert(!ACC16 || (NPASS == 1 && AUG), "fp16 accumulators exist for the 1-term kernel with the bias MMA");
     static_assert(NCTA == 1 || (NPASS == 1 && AUG && !SCORES), "the CTA-pair kernel exists for the 1-term AUG variant");
     if (p.gate_flag && *p.gate_flag != p.gate_want) return;     // uniform for the whole grid
     // bias through the MMA (AUG): only with one term (shared memory for the extra tile) and while the fp16
     // pieces of the bias plane can represent every S*|c_k|^2.  That is a device-side fact, so the host launches
     // the AUG and the plain variant back to back and exactly one of them runs (uniform for the whole grid).
     constexpr bool aug = AUG;
-    if (p.use_bias_mma && AUG != (__uint_as_float(p.stats->cn_max_bits) < kBiasMax)) return;
+    if (!ACC16 && p.use_bias_mma && AUG != (__uint_as_float(p.stats->cn_max_bits) < kBiasMax)) return;
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t smem_base = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -536,6 +587,12 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         const float inv_s = 1.f / (sigma_x * sigma_c);
         const float cmax = __uint_as_float(p.stats->c_normmax_bits);
         const float clomax = __uint_as_float(p.stats->c_lonormmax_bits);
+        // fp16-accumulator tier: its scores are rho16 times those of the fp32 kernels (a smaller power-of-two centroid
+        // scale keeps every partial sum inside the fp16 range)
+        const float rho16 = ACC16 ? p.stats->rho16 : 1.f;
+        const float inv_s16 = inv_s / rho16;
+        const float cnmax = __uint_as_float(p.stats->cn_max_bits);
+        (void)inv_s16; (void)cnmax;
         uint32_t ac = 0;
         // row norms of the NEXT row tile are fetched while the current one is scanned
         auto tile_row = [&](int it) { return (int64_t)tile_of(it) * kTcBlockM + q * 32 + lane; };
@@ -552,7 +609,11 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 nn_next = *reinterpret_cast<const float2*>(p.xnorm + 2 * tile_row(it + 1));
             // certified if the two best scores are further apart than twice the score error bound:
             // 3 terms: operand split + accumulator truncation; 1 term: the dropped x_lo.c and x.c_lo too
-            const float thr = (NPASS == 3) ? 2.f * p.gamma * xn * cmax
+            // fp16 accumulators: every MMA instruction rounds the accumulator to fp16 (2^-11 of its magnitude, which
+            // is at most rho16 * (max_k S|c_k|^2 + |X'_i| max_k |C'_k|)), on top of the dropped low-order terms of the
+            // 1-term kernel
+            const float thr = ACC16 ? 2.f * rho16 * (xlo * cmax + xn * clomax + p.gamma16 * (cnmax + xn * cmax))
+                            : (NPASS == 3) ? 2.f * p.gamma * xn * cmax
                                            : 2.f * (xlo * cmax + xn * clomax + p.gamma1 * xn * cmax);
             // 3 terms: offset by ~S*|x|^2 so that scores are S*d >= 0 and the index packing truncates
             // 2^-16 of a SMALL number; with 1 term the threshold is far above that truncation anyway
@@ -563,6 +624,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             float ga[kEpiG];                                                // partition epilogue
 #pragma unroll
             for (int g = 0; g < kEpiG; ++g) ga[g] = INFINITY;
+            uint32_t gh[kH2Cells];                                          // ... of the fp16-accumulator tier (half2 bits)
+#pragma unroll
+            for (int g = 0; g < kH2Cells; ++g) gh[g] = 0x7C007C00u;         // (+inf, +inf)
             Top2 tb = {INFINITY, INFINITY};
             int a_blk = 0;
             for (int nt = 0; nt < p.n_ntiles; ++nt, ++ac) {
@@ -593,6 +657,36 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 const float e_in = te.m1, o_in = to.m1, b_in = tb.m1;
                 const int kbase = nt * BN + half * kCols;
                 uint32_t ra[32], rb[32];
+#ifdef KMC_ABL_NO_EPI
+                if (p.n < 0) {
+#endif
+                if constexpr (ACC16) {
+                    static_assert(!ACC16 || kCols == 128, "two packed loads of 64 columns per warp and tile");
+                    tmem_ld_32x64_pack16(taddr, ra);
+                    tmem_ld_wait_dep(ra);
+                    tmem_ld_32x64_pack16(taddr + 64, rb);
+                    if constexpr (SCORES) {
+                        if (score_row) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                if (kbase + 2 * i < p.K) score_row[kbase + 2 * i] = __low2float(as_h2(ra[i])) * inv_s16;
+                                if (kbase + 2 * i + 1 < p.K) score_row[kbase + 2 * i + 1] = __high2float(as_h2(ra[i])) * inv_s16;
+                            }
+                        }
+                    }
+                    epi_chunk_h2(ra, 0, 0xFFFFFFFCu, gh, tb);
+                    tmem_ld_wait_dep(rb);
+                    if constexpr (SCORES) {
+                        if (score_row) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                if (kbase + 64 + 2 * i < p.K) score_row[kbase + 64 + 2 * i] = __low2float(as_h2(rb[i])) * inv_s16;
+                                if (kbase + 64 + 2 * i + 1 < p.K) score_row[kbase + 64 + 2 * i + 1] = __high2float(as_h2(rb[i])) * inv_s16;
+                            }
+                        }
+                    }
+                    epi_chunk_h2(rb, 2, 0xFFFFFFFCu, gh, tb);
+                } else {
                 tmem_ld_32x32(taddr, ra);
 #pragma unroll
                 for (int cc = 0; cc < kCols / 32; cc += 2) {
@@ -612,6 +706,10 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         epi_chunk_part<NPASS == 3, !AUG>(rb, cn + (cc + 1) * 32, off, (cc + 1) * 32 / kEpiG, p.blk_mask,
                                                          ga, tb);
                 }
+                }
+#ifdef KMC_ABL_NO_EPI
+                }
+#endif
                 tc_fence_before_sync();
                 __syncwarp();
                 if (threadIdx.x == 128) KMC_TRACE_AT(ac, 3);
@@ -622,12 +720,70 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 if (__float_as_uint(te.m1) != __float_as_uint(e_in)) a_e = kbase + (int)(__float_as_uint(te.m1) & 0x7Fu);
                 if (__float_as_uint(to.m1) != __float_as_uint(o_in)) a_o = kbase + (int)(__float_as_uint(to.m1) & 0x7Fu);
                 if (__float_as_uint(tb.m1) != __float_as_uint(b_in))
-                    a_blk = kbase + (int)(__float_as_uint(tb.m1) & (uint32_t)(kEpiBlocksPerHalf - 1)) * kEpiG;
+                    a_blk = ACC16 ? kbase + (int)(__float_as_uint(tb.m1) & 3u) * 32
+                                  : kbase + (int)(__float_as_uint(tb.m1) & (uint32_t)(kEpiBlocksPerHalf - 1)) * kEpiG;
             }
             if (threadIdx.x == 128) KMC_TRACE_AT((uint32_t)(it + 1) * (uint32_t)p.n_ntiles - 1u, 4);
             float m1, m2;
             int a1;
-            if constexpr (SCORES || kOldEpi) {
+            if constexpr (ACC16) {
+                // 32 cells (cell g = low half of register g, cell 16+g = its high half), all reductions as half2
+                // trees: best = smallest cell; the cells that hold it; second best = the smaller of the best OTHER
+                // cell and the second-smallest block minimum (= the best again if two cells tie)
+                uint32_t t8[8];
+#pragma unroll
+                for (int g = 0; g < 8; ++g) t8[g] = h2min(gh[g], gh[8 + g]);
+                uint32_t tm = h2min(h2min(h2min(t8[0], t8[1]), h2min(t8[2], t8[3])), h2min(h2min(t8[4], t8[5]), h2min(t8[6], t8[7])));
+                const __half m1h = __hmin(__low2half(as_h2(tm)), __high2half(as_h2(tm)));
+                m1 = __half2float(m1h);
+                const __half2 m1h2 = __half2half2(m1h);
+                uint32_t hits = 0, ex[kH2Cells];
+#pragma unroll
+                for (int g = 0; g < kH2Cells; ++g) {
+                    const uint32_t eq = __heq2_mask(as_h2(gh[g]), m1h2);          // 0xFFFF per equal half
+                    hits |= (eq & 0x00010001u) << g;
+                    ex[g] = gh[g] | (eq & 0x7E007E00u);                           // equal halves -> NaN: ignored by min
+                }
+#pragma unroll
+                for (int g = 0; g < 8; ++g) t8[g] = h2min(ex[g], ex[8 + g]);
+                tm = h2min(h2min(h2min(t8[0], t8[1]), h2min(t8[2], t8[3])), h2min(h2min(t8[4], t8[5]), h2min(t8[6], t8[7])));
+                const float others = fminf(__low2float(as_h2(tm)), __high2float(as_h2(tm)));   // NaN (no other cell) -> ignored
+                const bool tie = (hits & (hits - 1u)) != 0u;
+                m2 = tie ? m1 : fminf(tb.m2, others);
+                // column of the best: block of the smallest block minimum (its number sits in two mantissa bits that
+                // an fp16 value leaves zero) and the cell that holds the best value.  Two such cells (equal fp16
+                // scores): which of them lies in that block cannot be told here, so the label carries both columns
+                // and the refine, which gets every such row (m2 = m1), starts from the nearer one.
+                auto col_of = [](int c) { return c < 16 ? 2 * c : 2 * (c - 16) + 1; };
+                const int c1 = hits ? __ffs(hits) - 1 : 0;
+                a1 = a_blk + col_of(c1);
+                const uint32_t rest = hits & (hits - 1u);
+                if (tie) a1 |= (col_of(__ffs(rest) - 1) + 1) << 26;
+                // three or more cells with the best value (4 rows in 10^4 at config 4): the label has room for two
+                // candidates, so the warp settles these rows here with exact distances of the tied columns
+                unsigned need = __ballot_sync(0xffffffffu, (rest & (rest - 1u)) != 0u && row_ok);
+                while (need) {
+                    const int src = __ffs(need) - 1;
+                    need &= need - 1u;
+                    const int64_t r_s = __shfl_sync(0xffffffffu, row, src);
+                    const uint32_t h_s = __shfl_sync(0xffffffffu, hits, src);
+                    const int b_s = __shfl_sync(0xffffffffu, a_blk, src);
+                    float bd = INFINITY;
+                    int bkk = b_s;
+                    for (uint32_t h = h_s; h; h &= h - 1u) {
+                        const int k = b_s + col_of(__ffs(h) - 1);
+                        if (k >= p.K) continue;
+                        float acc = 0.f;
+                        for (int j = lane; j < p.D; j += 32) {
+                            const float dd = p.x[r_s * p.D + j] - p.cent[(int64_t)k * p.D + j];
+                            acc = fmaf(dd, dd, acc);
+                        }
+                        acc = warp_sum(acc);
+                        if (acc < bd) { bd = acc; bkk = k; }
+                    }
+                    if (lane == src) a1 = bkk;
+                }
+            } else if constexpr (SCORES || kOldEpi) {
                 // merge the two chains of this thread ...
                 if (to.m1 < te.m1) { m1 = to.m1; a1 = a_o; m2 = fminf(te.m1, to.m2); }
                 else { m1 = te.m1; a1 = a_e; m2 = fminf(to.m1, te.m2); }
@@ -705,11 +861,11 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
             if (half == 0) {                                 // warp-uniform
                 bool amb = false;
                 if (row_ok) {
-                    if (a1 >= p.K) a1 = 0;
+                    if ((int)((uint32_t)a1 & kAnchorMask) >= p.K) a1 = 0;
                     p.labels[row] = a1;
-                    const float pack_err = ((SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));
+                    const float pack_err = ACC16 ? 0.f : ((SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));
                     float thr_row = thr;
-                    if (NPASS == 1) {
+                    if (NPASS == 1 && !ACC16) {
                         // Tighter bound on the dropped x_lo.(c_k - c_b): |c_k - c_b| <= |x - c_k| + |x - c_b|, and the
                         // distances follow from the scores themselves (P = score + S|x|^2 = S*d, each known to
                         // +-thr/2).  The right-hand side grows more slowly in the score of k than the gap does, so
@@ -723,6 +879,9 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         if (r2 > rho) thr_row = fminf(thr, tight);                // (monotonicity needs r > rho / 2)
                     }
                     amb = p.worklist && !((m2 - m1) > thr_row + pack_err);        // NaNs count as uncertified
+#ifdef KMC_ABL_NO_B
+                    amb = false;
+#endif
                 }
                 // uncertified rows: one 32-bit mask per warp and row tile, no atomic and no dependent store on
                 // this path (a returning atomic here costs ~800 cycles per row tile in warps that hold two of the
@@ -784,6 +943,13 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
     KMC_TRY(make_map(fn, &c->tmap_c_half, c->at<void>(c->off_cplanes), (uint64_t)c->D_pad, (uint64_t)(2 * c->K_pad),
                      kTcBlockN / 2));
     KMC_TRY(make_map(fn, &c->tmap_bias_half, c->at<void>(c->off_cbias), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN / 2,
+                     kBiasCols, CU_TENSOR_MAP_SWIZZLE_32B));
+    // fp16-accumulator tier: one centroid plane and a bias plane at their own scale
+    KMC_TRY(make_map(fn, &c->tmap_c16, c->at<void>(c->off_cplane16), (uint64_t)c->D_pad, (uint64_t)c->K_pad, kTcBlockN));
+    KMC_TRY(make_map(fn, &c->tmap_bias16, c->at<void>(c->off_cbias16), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN, kBiasCols,
+                     CU_TENSOR_MAP_SWIZZLE_32B));
+    KMC_TRY(make_map(fn, &c->tmap_c16_half, c->at<void>(c->off_cplane16), (uint64_t)c->D_pad, (uint64_t)c->K_pad, kTcBlockN / 2));
+    KMC_TRY(make_map(fn, &c->tmap_bias16_half, c->at<void>(c->off_cbias16), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN / 2,
                      kBiasCols, CU_TENSOR_MAP_SWIZZLE_32B));
     // ... or its half of a 128-centroid stage (four accumulator tiles)
     KMC_TRY(make_map(fn, &c->tmap_c_quarter, c->at<void>(c->off_cplanes), (uint64_t)c->D_pad, (uint64_t)(2 * c->K_pad),
@@ -928,6 +1094,37 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
     };
     TcParams pp = p;
     pp.use_bias_mma = 0;
+    if (terms == 16) {
+        // fp16 accumulators (1 term, bias through the MMA at this tier's own scale): its own centroid / bias maps
+        auto launch16 = [&](auto kern, uint32_t smem_bytes) -> int {
+            KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c16, c->tmap_bias16, pp);
+            KMC_CUDA(cudaGetLastError());
+            c->launches++;
+            return 0;
+        };
+        if (p.scores) return launch16(tc_assign_kernel<KC, true, 1, 8, true, 1, 256, true>, TcCfg<KC, 1>::kSmemBytes);
+        if (c->tc_pair && p.n_mtiles >= 2 && p.n_ntiles * KC >= 4) {
+            auto kern = tc_assign_kernel<KC, false, 1, 8, true, 2, 256, true>;
+            const uint32_t smem_bytes = TcCfg<KC, 1, 2, 256>::kSmemBytes;
+            KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            const int pairs_needed = (p.n_mtiles + 1) / 2, pairs_max = c->sm_count / 2;
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)(2 * (pairs_needed < pairs_max ? pairs_needed : pairs_max)));
+            cfg.blockDim = dim3((unsigned)threads);
+            cfg.dynamicSmemBytes = smem_bytes;
+            cfg.stream = s;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c16_half, c->tmap_bias16_half, pp));
+            c->launches++;
+            return 0;
+        }
+        return launch16(tc_assign_kernel<KC, false, 1, 8, true, 1, 256, true>, TcCfg<KC, 1>::kSmemBytes);
+    }
     if (p.scores) return launch(tc_assign_kernel<KC, true, 3, 8, false, 1>, TcCfg<KC, 3>::kSmemBytes, pp);
     if (terms != 1) return launch(tc_assign_kernel<KC, false, 3, 8, false, 1>, TcCfg<KC, 3>::kSmemBytes, pp);
 #ifdef KMC_NO_BIAS_MMA      // A/B build: biases added by the epilogue (FADD per score) instead of the extra MMA step
@@ -973,6 +1170,9 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.scores = scores_out;
     p.gamma = (float)c->tc_gamma;
     p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);
+    // one rounding to fp16 (2^-11 of the accumulator, round to nearest) per MMA instruction of a tile, 25 % head-room;
+    // measured on the GPU (tools/check_acc16.py): the largest score error is 0.47 of this bound
+    p.gamma16 = (float)(1.25 * ((double)(c->D_pad / 16) + 1.0) / 2048.0);
     p.pack_mask = 0xFFFFFF80u;
     p.blk_mask = ~(uint32_t)(kEpiBlocksPerHalf - 1);
     p.x = c->points;

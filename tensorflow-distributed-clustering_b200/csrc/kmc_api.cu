@@ -56,6 +56,8 @@ static void layout_workspace(kmc_ctx* c) {
         c->off_cnorm = take(c->K_pad * 4);
         c->off_cbias = take(c->K_pad * kBiasCols * 2);   // S*|c_k|^2 as fp16 pieces: one extra MMA k-step adds it
         c->off_cplanes = take(2 * c->K_pad * c->D_pad * 2);
+        c->off_cplane16 = take(c->K_pad * c->D_pad * 2);     // fp16-accumulator tier: hi plane at its own scale
+        c->off_cbias16 = take(c->K_pad * kBiasCols * 2);
         c->off_ccdist = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;   // pruning table of the refine pass
         if (c->K <= 8192) c->off_overflow = take(c->n * 4);            // rows whose refine walk hit its cap
         c->off_nbr = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;      // ... sorted nearest-first per centroid
@@ -704,7 +706,8 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             c->tc_gamma = value;
             return 0;
         case KMC_PARAM_TC_TERMS:
-            if (value != 0.0 && value != 1.0 && value != 3.0) KMC_FAIL(KMC_E_INVALID, "tensor terms must be 0, 1 or 3");
+            if (value != 0.0 && value != 1.0 && value != 3.0 && value != 16.0)
+                KMC_FAIL(KMC_E_INVALID, "tensor terms must be 0, 1, 3 or 16 (1 term, fp16 accumulators)");
             c->tc_terms = (int)value;
             return 0;
         case KMC_PARAM_REFINE_KERNEL:
@@ -776,7 +779,7 @@ int kmc_debug_tc_scores(kmc_ctx* c, float* dev_scores, void* stream) {
     KMC_CUDA(cudaSetDevice(c->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     KMC_TRY(ensure_planes(c, s));
-    return launch_tc_assign(c, c->labels(), nullptr, &c->stats()->n_amb[0], dev_scores, 0, c->n, 3, nullptr, 0u, s);
+    return launch_tc_assign(c, c->labels(), nullptr, &c->stats()->n_amb[0], dev_scores, 0, c->n, c->tc_terms == 16 ? 16 : 3, nullptr, 0u, s);
 }
 
 }  // extern "C"

@@ -61,6 +61,7 @@ struct DeviceStats {
     float sigma_c;                    // power-of-two scale of the centroid planes (x -2 folded)
     unsigned int c_lonormmax_bits;    // max_k |C' - C'_hi| (scaled units): bound for the 1-term kernel
     unsigned int cn_max_bits;         // max_k S*|c_k|^2 (fp32 bits): the bias plane is valid below 2^31
+    float rho16;                      // fp16-accumulator tier: its centroid scale / sigma_c (a power of two <= 1)
     unsigned int tc3_flag[kMaxChunks];      // set by the gate: the 3-term kernel redoes this chunk in this pass
     unsigned int tc_skip[kMaxChunks];       // passes for which the chunk goes straight to the 3-term kernel
     unsigned int tc_period[kMaxChunks];     // length of the next skip period (1, 2, 4 ... 16)
@@ -89,7 +90,8 @@ struct kmc_ctx {
     // tensor-path geometry
     int64_t D_pad = 0, K_pad = 0;
     double tc_gamma = 0.0;
-    int tc_terms = 0;                   // KMC_PARAM_TC_TERMS: 0 = adaptive, 1 or 3 = fixed
+    int tc_terms = 0;                   // KMC_PARAM_TC_TERMS: 0 = adaptive, 1 or 3 = fixed, 16 = 1 term with fp16 accumulators
+    bool tc_acc16 = false;              // KMC_PARAM_TC_ACC16: adaptive policy starts with the fp16-accumulator tier
     int n_chunks = 1;                   // row chunks per accumulate pass (tensor path, large shards)
     cudaStream_t side_stream = nullptr; // refine + accumulation of chunk c run here while chunk c+1 is assigned
     cudaEvent_t chunk_done[kmc::kMaxChunks] = {};
@@ -107,7 +109,7 @@ struct kmc_ctx {
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_labels2 = 0, off_perm = 0,
             off_changed = 0, off_running = 0, off_overflow = 0,
             off_sort = 0, sort_stride = 0, sort_cursor = 0, sort_offsets = 0, sort_segoff = 0,
-            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0, off_ambmask = 0,
+            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0, off_ambmask = 0, off_cplane16 = 0, off_cbias16 = 0,
             off_ccdist = -1, off_nbr = -1;
     const float* points = nullptr;
     // incremental accumulation: two label buffers (this pass / previous pass), running fp64 sums and counts
@@ -128,6 +130,7 @@ struct kmc_ctx {
     alignas(64) CUtensorMap tmap_bias;
     alignas(64) CUtensorMap tmap_c_half;      // 128-row boxes: the halves of a centroid stage a CTA pair loads
     alignas(64) CUtensorMap tmap_bias_half;
+    alignas(64) CUtensorMap tmap_c16, tmap_bias16, tmap_c16_half, tmap_bias16_half;   // fp16-accumulator tier
     alignas(64) CUtensorMap tmap_c_quarter;   // 64-row boxes: a CTA's half of a 128-centroid stage
     alignas(64) CUtensorMap tmap_bias_quarter;
     int tc_tile_n = 256;                      // KMC_PARAM_TC_TILE_N: centroids per accumulator tile of the pair kernel
@@ -215,5 +218,16 @@ int launch_prep_centroids(kmc_ctx* c, cudaStream_t s);
 int launch_centroid_absmax(kmc_ctx* c, cudaStream_t s);
 
 __host__ __device__ inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// Labels of UNCERTIFIED rows between the tensor kernel and the refine may carry a second anchor candidate: the
+// fp16-accumulator tier cannot tell which of two columns of one 32-column block holds the best score when their
+// fp16 scores are equal, so it stores the first column as the label (bits 0-25) and the second one's position in
+// the block, plus one, in bits 26-31.  The refine starts from the nearer of the two and rewrites the label.
+constexpr uint32_t kAnchorMask = 0x03FFFFFFu;
+__host__ __device__ inline int anchor_first(int32_t lab) { return (int)((uint32_t)lab & kAnchorMask); }
+__host__ __device__ inline int anchor_second(int32_t lab) {
+    const uint32_t c = (uint32_t)lab >> 26;
+    return c ? (int)((((uint32_t)lab & kAnchorMask) & ~31u) + (c - 1u)) : -1;
+}
 
 }  // namespace kmc

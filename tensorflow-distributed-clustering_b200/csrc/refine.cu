@@ -108,7 +108,9 @@ refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent
     const int64_t n_work = (int64_t)(*n_work_dev);
     for (int64_t w = warp; w < n_work; w += nwarps) {
         const int64_t row = worklist[w];
-        const int a = labels[row];
+        const int32_t lab = labels[row];
+        int a = anchor_first(lab);
+        const int a_alt = anchor_second(lab);
         float xr[NPL];
 #pragma unroll
         for (int q = 0; q < NPL; ++q) {
@@ -125,6 +127,7 @@ refine_kernel(const float* __restrict__ x, int D, const float* __restrict__ cent
             }
             return warp_sum(acc);
         };
+        if (a_alt >= 0 && a_alt < K && dist_to(a_alt) < dist_to(a)) a = a_alt;     // two anchor candidates: the nearer
         float best = dist_to(a);
         int bk = a;
         // a small relative margin absorbs the fp32 rounding of ccdist and of `best`
@@ -185,13 +188,34 @@ refine4_kernel(const float* __restrict__ x, int D, const float* __restrict__ cen
     for (int64_t w = warp; w < n_work; w += nwarps) {
         ++rows_done;
         const int64_t row = worklist[w];
-        const int a = labels[row];
+        const int32_t lab = labels[row];
+        int a = anchor_first(lab);
+        const int a_alt = anchor_second(lab);
         float4 xr[NV];
         const float4* xp = reinterpret_cast<const float4*>(x + row * D);
 #pragma unroll
         for (int q = 0; q < NV; ++q) {
             const int v = t + 8 * q;
             xr[q] = v < nvec ? xp[v] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (a_alt >= 0 && a_alt < K) {          // two anchor candidates (warp-uniform): lane groups 0 / 1 measure them
+            const int kc = (g & 1) ? a_alt : a;
+            const float4* cp = reinterpret_cast<const float4*>(cent + (int64_t)kc * D);
+            float acc = 0.f;
+#pragma unroll
+            for (int q = 0; q < NV; ++q) {
+                const int v = t + 8 * q;
+                if (v < nvec) {
+                    const float4 cv = cp[v];
+                    const float d0 = xr[q].x - cv.x, d1 = xr[q].y - cv.y, d2 = xr[q].z - cv.z, d3 = xr[q].w - cv.w;
+                    acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+                }
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            const float da = __shfl_sync(0xffffffffu, acc, 0), dalt = __shfl_sync(0xffffffffu, acc, 8);
+            if (dalt < da) a = a_alt;
         }
         const float* ccrow = cc + (int64_t)a * K;
         const int32_t* nbrow = nbr + (int64_t)a * K;
@@ -310,13 +334,23 @@ refine8_kernel(const float* __restrict__ x, int D, const float* __restrict__ cen
         const bool live = w < n_work;
         if (live) { ++rows_done; walked += 2; }
         const int64_t row = live ? worklist[w] : 0;
-        const int a = live ? labels[row] : 0;
+        const int32_t lab = live ? labels[row] : 0;
+        int a = anchor_first(lab);
+        int a_alt = anchor_second(lab);
+        if (a_alt >= K) a_alt = -1;
         float4 xr[NV];
         const float4* xp = reinterpret_cast<const float4*>(x + row * D);
 #pragma unroll
         for (int q = 0; q < NV; ++q) {
             const int v = t + 8 * q;
             xr[q] = (live && v < nvec) ? ld_stream_f4(xp + v) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (__any_sync(0xffffffffu, a_alt >= 0)) {      // a row with two anchor candidates: its lane group takes the nearer
+            float da = group_dist<NV>(xr, cent, a_alt >= 0 ? a : -1, D, nvec, t);
+            float dalt = group_dist<NV>(xr, cent, a_alt, D, nvec, t);
+            da = group_sum8(da);
+            dalt = group_sum8(dalt);
+            if (a_alt >= 0 && dalt < da) a = a_alt;
         }
         const float* ccrow = cc + (int64_t)a * K;
         const int32_t* nbrow = nbr + (int64_t)a * K;

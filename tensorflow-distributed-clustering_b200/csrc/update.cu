@@ -99,14 +99,28 @@ int launch_centroid_absmax(kmc_ctx* c, cudaStream_t s) {
 // One warp per (padded) centroid row: C'_hi / C'_lo = split fp16 of (-2 * sigma_c * c), and
 // cn'[k] = sigma_x * sigma_c * |c_k|^2 (3e38 for padding rows and NaN centroids, so they never
 // win), plus max_k |C'_k| for the refine threshold.
+// fp16-accumulator tier: a second, smaller centroid scale sigma_c16 = rho16 * sigma_c (power of two) such that no
+// partial sum of a score can leave the fp16 range: |S16 (|c_k|^2 - 2 x_i.c_k)| <= S16 * D * (cabs^2 + 2 xabs cabs)
+// < 24000 with S16 = sigma_x * sigma_c16 (the bound uses |v| <= sqrt(D) * absmax for rows and centroids alike).
+__device__ __forceinline__ float rho16_for(float sigma_x, float sigma_c, float xabs, float cabs, int D) {
+    const float bound = sigma_x * sigma_c * (float)D * (cabs * cabs + 2.f * xabs * cabs);
+    if (!(bound > 0.f) || !(bound < 3.0e38f)) return 1.f;
+    int e;
+    frexpf(bound / 24000.f, &e);          // bound / 24000 = f * 2^e, f in [0.5, 1)  ->  rho = 2^-e keeps bound * rho < 24000
+    e = e < 0 ? 0 : (e > 60 ? 60 : e);
+    return ldexpf(1.f, -e);
+}
+
 __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __restrict__ cent, int K, int D,
                                                              int K_pad, int D_pad, __half* __restrict__ chi,
                                                              __half* __restrict__ clo, float* __restrict__ cnorm,
-                                                             __half* __restrict__ cbias, DeviceStats* stats) {
+                                                             __half* __restrict__ cbias, __half* __restrict__ c16,
+                                                             __half* __restrict__ cbias16, DeviceStats* stats) {
     // 2*|c| < 2^14 after scaling: absmax of (2c)
     const float sigma_c = scale_from_absmax(2.f * __uint_as_float(stats->c_absmax_bits));
     const float sigma_x = stats->sigma_x;
-    if (blockIdx.x == 0 && threadIdx.x == 0) stats->sigma_c = sigma_c;
+    const float rho16 = rho16_for(sigma_x, sigma_c, __uint_as_float(stats->x_absmax_bits), __uint_as_float(stats->c_absmax_bits), D);
+    if (blockIdx.x == 0 && threadIdx.x == 0) { stats->sigma_c = sigma_c; stats->rho16 = rho16; }
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -139,6 +153,7 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
             hr[j] = h;
             lr[j] = __float2half_rn(r);
             ss_lo = fmaf(r, r, ss_lo);
+            c16[(int64_t)k * D_pad + j] = __float2half_rn(v * rho16);      // = rho16 * h unless it goes subnormal
         }
         ss_lo = warp_sum(ss_lo);
         // bias plane: row k = fp16 pieces p_i with sum_i a_i * p_i = cn (a = kBiasConst), zero padded to one
@@ -158,7 +173,20 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
                     r -= (double)kBiasConst[i] * (double)__half2float(h);
                 }
                 if (!dead) atomicMax(&stats->cn_max_bits, __float_as_uint(cn));
+                // the same pieces at the scale of the fp16-accumulator tier; a dead row gets 49152 there, above every
+                // real score of that tier (< 24000) and inside the fp16 range
+                __half* br16 = cbias16 + (int64_t)k * kBiasCols;
+                double r16 = dead ? 49152.0 : (double)cn * (double)rho16;
+                for (int i = 0; i < kBiasPieces; ++i) {
+                    float q = (float)(r16 / (double)kBiasConst[i]);
+                    q = fminf(fmaxf(q, -65504.f), 65504.f);
+                    const __half h = __float2half_rn(q);
+                    br16[i] = h;
+                    r16 -= (double)kBiasConst[i] * (double)__half2float(h);
+                }
             }
+            __syncwarp();
+            if (lane >= kBiasPieces && lane < kBiasCols) cbias16[(int64_t)k * kBiasCols + lane] = __float2half_rn(0.f);
         }
         if (lane == 0) {
             cnorm[k] = dead ? 3.0e38f : cn;
@@ -183,7 +211,8 @@ int launch_prep_centroids(kmc_ctx* c, cudaStream_t s) {
     __half* clo = chi + c->K_pad * c->D_pad;
     prep_centroids_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->centroids(), (int)c->K, (int)c->D, (int)c->K_pad,
                                                            (int)c->D_pad, chi, clo, c->at<float>(c->off_cnorm),
-                                                           c->at<__half>(c->off_cbias), c->stats());
+                                                           c->at<__half>(c->off_cbias), c->at<__half>(c->off_cplane16),
+                                                           c->at<__half>(c->off_cbias16), c->stats());
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;

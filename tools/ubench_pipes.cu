@@ -38,6 +38,8 @@ __global__ void bench(float* out, unsigned long long* cycles, float seed) {
             if (OP == 11) v[c] = fmaf(v[c], w, z);                       // FFMA
             if (OP == 12) u[c] = (v[c] < w) ? u[c] : uz, v[c] += 1.f;    // FSETP + SEL + FADD
             if (OP == 13) { float2 t = __fadd2_rn(make_float2(v[c], __uint_as_float(u[c])), make_float2(w, z)); v[c] = t.x; u[c] = __float_as_uint(t.y); }   // FADD2
+            if (OP == 15) h[c] = __hmin2(__hmin2(h[c], hw), __halves2half2(__low2half(hw), __high2half(h[(c + 1) % CHAINS])));   // VHMNMX (3-input half2 min)
+            if (OP == 16) { h[c] = __hmin2(h[c], hw); h[c] = __hmin2_nan(h[c], __halves2half2(__low2half(hw), __high2half(h[(c + 1) % CHAINS]))); }   // HMNMX2 + HMNMX2.NAN: two instructions the assembler cannot fuse
             if (OP == 14) { float2 t = __ffma2_rn(make_float2(v[c], __uint_as_float(u[c])), make_float2(w, z), make_float2(z, w)); v[c] = t.x; u[c] = __float_as_uint(t.y); }   // FFMA2
         }
         if (OP == 0 || OP == 7 || OP == 1) { w += 1e-7f; }
@@ -70,6 +72,7 @@ int main() {
         run<2>("FADD", warps); run<11>("FFMA", warps); run<7>("FMNMX", warps); run<1>("FMNMX3", warps);
         run<0>("FADD+FMNMX", warps); run<3>("LOP3", warps); run<6>("IMNMX(u32)", warps); run<4>("VIMNMX3.s32", warps);
         run<9>("VIMNMX3.s16x2", warps); run<10>("vminu2", warps); run<5>("HMNMX2", warps); run<8>("IMAD", warps);
+        run<15>("VHMNMX (min3 half2)", warps); run<16>("HMNMX2 + HMNMX2.NAN pair", warps);
         run<12>("FSETP+SEL+FADD", warps); run<13>("FADD2 (2 adds/inst)", warps); run<14>("FFMA2 (2 fmas/inst)", warps);
         printf("\n");
     }
