@@ -232,10 +232,13 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
 /* Tunable parameters (advanced; defaults are chosen at kmc_create). */
 #define KMC_PARAM_TC_GAMMA  1   /* relative error bound of the split-fp16 tensor scores used to
                                    decide which rows go to the exact refine kernel */
-#define KMC_PARAM_TC_TERMS  3   /* tensor path: MMA terms per score. 1 = hi*hi only + exact refine of every
-                                   uncertified row; 3 = fp32-accurate split; 0 (default) = start with 1 and fall
-                                   back to 3 on the device when the refine of the uncertified rows would cost more
-                                   (long candidate walks and more than 3% of the rows uncertified) */
+#define KMC_PARAM_TC_TERMS  3   /* tensor path: MMA terms per score. 1 = hi*hi only (fp32 accumulators) + exact refine
+                                   of every uncertified row; 16 = the same term with fp16 accumulators (packed TMEM
+                                   reads, half2 epilogue: the cheapest pass, the widest certification margin);
+                                   3 = fp32-accurate split; 0 (default) = start with 16 (K > 256, see
+                                   KMC_PARAM_TC_ACC16) or 1 and fall back to 3 on the device when the refine of the
+                                   uncertified rows would cost more.  Final labels are the same exact fp32 argmin
+                                   whatever the tier */
 #define KMC_PARAM_PROFILE   2   /* non-zero: record CUDA events around each phase (see below) */
 #define KMC_PARAM_REFINE_KERNEL 4 /* exact refine of uncertified rows: 4 = warp per row (long candidate walks),
                                    8 = eight lanes per row (short walks), 0 (default) = both enqueued, the
@@ -252,6 +255,8 @@ int kmc_read_stats(kmc_ctx* ctx, double* host_stats, void* stream);
 #define KMC_PARAM_DELTA_ATOMIC_ROWS 9 /* incremental accumulation: an iteration that changed at most this many labels
                                    applies the changed rows to the running sums with fp64 atomics (one launch) instead
                                    of the sort + segmented sum (ten); 0 = never, negative = the default (2^21 / D) */
+#define KMC_PARAM_TC_ACC16 10  /* 1 (default): the adaptive policy's first tier uses fp16 accumulators where K > 256;
+                                   0: fp32 accumulators everywhere */
 int kmc_set_param(kmc_ctx* ctx, int param, double value);
 
 /*

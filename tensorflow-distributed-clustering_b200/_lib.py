@@ -30,6 +30,7 @@ KMC_PARAM_INCREMENTAL = 6
 KMC_PARAM_TC_PAIR = 7
 KMC_PARAM_TC_TILE_N = 8
 KMC_PARAM_DELTA_ATOMIC_ROWS = 9
+KMC_PARAM_TC_ACC16 = 10
 KMC_PHASE_COUNT = 5
 PATH_NAMES = {KMC_PATH_SMALL: "small", KMC_PATH_SIMT: "simt", KMC_PATH_TC: "tc"}
 PATH_FLAGS = {"auto": KMC_PATH_AUTO, "small": KMC_PATH_SMALL, "simt": KMC_PATH_SIMT, "tc": KMC_PATH_TC}

@@ -62,6 +62,8 @@ struct TcParams {
     unsigned long long* amb_counter;
     const unsigned int* gate_flag;   // null, or: run only if *gate_flag == gate_want (device-side precision policy)
     unsigned int gate_want;
+    const unsigned int* gate2;       // null, or a second condition of the same kind
+    unsigned int gate2_want;
     const float* xnorm;
     const float* cnorm;
     DeviceStats* stats;
@@ -90,7 +92,7 @@ struct TcParams {
 // config 5 slice: 95.7 against 79.1): twice as many tile steps, each with its fixed hand-off and bookkeeping cost,
 // outweigh the deeper MMA / epilogue overlap -- the 256-wide kernel already runs into the board's power cap.
 // (One CTA per MMA cannot use N = 128 at all: A + B would need 8 KB of shared-memory reads per 64-cycle MMA.)
-template <int KC, int NPASS, int NCTA = 1, int BN = kTcBlockN> struct TcCfg {
+template <int KC, int NPASS, int NCTA = 1, int BN = kTcBlockN, bool ACC16 = false> struct TcCfg {
     static constexpr int kPlanes = (NPASS == 1) ? 1 : 2;
     static constexpr int kTBufs = (int)kTmemCols / BN;                // accumulator tiles in TMEM
     static constexpr uint32_t kStageBTotal = BN * 128;                // one stage: BN centroids x 64 columns
@@ -105,7 +107,9 @@ template <int KC, int NPASS, int NCTA = 1, int BN = kTcBlockN> struct TcCfg {
     // 1 term: a constant 128 x 16 fp16 tile (32-byte swizzled) holding kBiasConst in its first columns; multiplied
     // with a stage of the bias plane it makes the MMA add S*|c_k|^2 to the accumulator (no FADD per score in the
     // epilogue)
-    static constexpr uint32_t kAExtBytes = (NPASS == 1) ? kTcBlockM * 32 : 0;      // 128 rows x 32 B
+    // (fp16-accumulator tier: not a constant but the row tile's own 128 x 16 extension, one per points buffer)
+    static constexpr uint32_t kAExtTile = kTcBlockM * 32;                           // 128 rows x 32 B
+    static constexpr uint32_t kAExtBytes = ACC16 ? 4 * kAExtTile : (NPASS == 1) ? kAExtTile : 0;
     static constexpr uint32_t kOther = kBBytes + kAExtBytes + ((NPASS == 1) ? 8 * 128 * 4 + 1536 : 2 * kTcBlockN * 4) + 512;
     // the points tile is double buffered whenever two copies fit next to the B ring (227 KB per CTA)
     // ... and four deep for one-chunk tiles (D <= 64), whose short K sweep leaves little time per row tile to hide
@@ -347,8 +351,8 @@ template <int KC, bool SCORES, int NPASS, int EW, bool AUG, int NCTA, int BN = k
 __global__ void __maxnreg__(SCORES ? 128 : KMC_TC_MAXNREG)
 tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_constant__ CUtensorMap tm_xlo,
                  const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_bias,
-                 const TcParams p) {
-    using Cfg = TcCfg<KC, NPASS, NCTA, BN>;
+                 const __grid_constant__ CUtensorMap tm_xext, const TcParams p) {
+    using Cfg = TcCfg<KC, NPASS, NCTA, BN, ACC16>;
     static_assert(BN == kTcBlockN || (BN == 128 && NCTA == 2), "128-centroid tiles exist for CTA pairs only");
     constexpr int NB = Cfg::kTBufs;              // accumulator tiles in TMEM (2 or 4)
     // kind::f16, fp16 x fp16 -> fp32, A and B K-major, N = BN, M = 128 (one CTA) or 256 (the MMA a CTA pair shares)
@@ -362,6 +366,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     static_assert(!ACC16 || (NPASS == 1 && AUG), "fp16 accumulators exist for the 1-term kernel with the bias MMA");
     static_assert(NCTA == 1 || (NPASS == 1 && AUG && !SCORES), "the CTA-pair kernel exists for the 1-term AUG variant");
     if (p.gate_flag && *p.gate_flag != p.gate_want) return;     // uniform for the whole grid
+    if (p.gate2 && *p.gate2 != p.gate2_want) return;
     // bias through the MMA (AUG): only with one term (shared memory for the extra tile) and while the fp16
     // pieces of the bias plane can represent every S*|c_k|^2.  That is a device-side fact, so the host launches
     // the AUG and the plain variant back to back and exactly one of them runs (uniform for the whole grid).
@@ -403,7 +408,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         if (NCTA == 2) { tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols); tmem_relinquish_pair(); }
         else { tmem_alloc(smem_u32(tmem_slot), kTmemCols); tmem_relinquish(); }
     }
-    if (AUG) {
+    if (AUG && !ACC16) {
         // constant A tile of the bias step (128 rows x 16 fp16), in the 32-byte-swizzled K-major layout TMA
         // would produce: row r, 16-byte chunk c lives at r*32 + ((c ^ ((r >> 2) & 1)) << 4); only chunk 0 is non-zero
         uint4* ext = reinterpret_cast<uint4*>(smem + Cfg::kAExtOff);
@@ -449,13 +454,15 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 const int abuf = it % Cfg::kABufs;
                 const int m0 = tile_of(it) * kTcBlockM;
                 mbar_wait<200>(a_empty(abuf), (((uint32_t)it / Cfg::kABufs) & 1u) ^ 1u, p.stats, 0x100u + abuf);
-                if (leader) e_mbar_arrive_expect_tx(a_full(abuf), (uint32_t)NCTA * Cfg::kPlanes * KC * kTileBytesA);
+                if (leader) e_mbar_arrive_expect_tx(a_full(abuf), (uint32_t)NCTA * (Cfg::kPlanes * KC * kTileBytesA + (ACC16 ? Cfg::kAExtTile : 0u)));
 #pragma unroll
                 for (int pl = 0; pl < Cfg::kPlanes; ++pl)
 #pragma unroll
                     for (int kc = 0; kc < KC; ++kc)
                         load_tile(smem_base + ((abuf * Cfg::kPlanes + pl) * KC + kc) * kTileBytesA,
                                   pl == 0 ? &tm_xhi : &tm_xlo, kc * kTcChunkK, m0, a_full(abuf), kEvictFirst);
+                if (ACC16)       // the rows' extension for the bias step: constants + pieces of |X'|^2
+                    load_tile(smem_base + Cfg::kAExtOff + abuf * Cfg::kAExtTile, &tm_xext, 0, m0, a_full(abuf), kEvictFirst);
             };
             constexpr int kAhead = (Cfg::kABufs > 2) ? Cfg::kABufs - 1 : 1;      // row tiles requested ahead
             for (int j = 0; j < kAhead && j < n_my_tiles; ++j) load_a(j);
@@ -465,14 +472,15 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         if (nt == 0 && it + kAhead < n_my_tiles) load_a(it + kAhead);
                         continue;
                     }
-                    if (aug) {      // stage of the bias plane: 256 centroids x 16 columns (8 KB of the slot)
+                    auto load_bias_stage = [&]() {      // stage of the bias plane: 256 centroids x 16 columns (8 KB of the slot)
                         const int slot = pslot;
                         mbar_wait<100>(b_empty(slot), ppar, p.stats, 0x280u + slot);
                         if (leader) e_mbar_arrive_expect_tx(b_full(slot), Cfg::kBiasStageTotal);
                         load_tile(smem_base + Cfg::kABytes + slot * Cfg::kStageB, &tm_bias, 0,
                                   nt * BN + (int)cta_rank * (BN / NCTA), b_full(slot), kEvictLast);
                         pnext();
-                    }
+                    };
+                    if (aug && !ACC16) load_bias_stage();      // (fp16 accumulators: the bias step comes LAST, see the issuer)
                     for (int kc = 0; kc < KC; ++kc) {
 #pragma unroll
                         for (int pl = 0; pl < ((NPASS == 1) ? 1 : 2); ++pl) {
@@ -485,6 +493,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                             pnext();
                         }
                     }
+                    if (aug && ACC16) load_bias_stage();
                     // prefetch the next row tile's points as early as its buffer can be free
                     const int pf_after = (Cfg::kABufs >= 2) ? 0 : p.n_ntiles - 1;
                     if (nt == pf_after && it + kAhead < n_my_tiles) load_a(it + kAhead);
@@ -525,15 +534,20 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                     tc_fence_after_sync();
                     const uint32_t d_tmem = tmem_base + buf * BN;
                     uint32_t accum = 0;
-                    if (aug) {      // accumulator := S*|c_k|^2 (one k-step: constants x bias pieces)
+                    // bias step (one k-step of 16): constants x pieces of S|c_k|^2 -- and, with fp16 accumulators,
+                    // pieces of |X'_i|^2 x constants, so that the accumulator ends at S16 |x_i - c_k|^2.  With fp16
+                    // accumulators it comes LAST: until then the accumulator holds partial dot products only, the
+                    // smallest magnitudes (and fp16 rounding steps) the sum can go through.
+                    auto bias_step = [&](uint64_t a_ext_desc) {
                         const int slot = mslot;
                         mbar_wait<20>(b_full(slot), mpar, p.stats, 0x580u + slot);
                         tc_fence_after_sync();
-                        mma(d_tmem, ext_desc, bias_desc0 + (uint64_t)(slot * (int)(Cfg::kStageB >> 4)), 0);
+                        mma(d_tmem, a_ext_desc, bias_desc0 + (uint64_t)(slot * (int)(Cfg::kStageB >> 4)), accum);
                         accum = 1;
                         if (!b_resident) commit(b_empty(slot));
                         mnext();
-                    }
+                    };
+                    if (aug && !ACC16) bias_step(ext_desc);
                     for (int kc = 0; kc < KC; ++kc) {
                         // stage with the centroid hi plane: x_hi*c_hi, then x_lo*c_hi
                         int slot = mslot;
@@ -565,6 +579,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         if (!b_resident) commit(b_empty(slot));
                         mnext();
                     }
+                    if (aug && ACC16) bias_step(umma_desc_sw32(smem_base + Cfg::kAExtOff + abuf * Cfg::kAExtTile));
                     commit(t_full(buf));
                     KMC_TRACE_AT(ac, 7);
                 }
@@ -591,8 +606,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
         // scale keeps every partial sum inside the fp16 range)
         const float rho16 = ACC16 ? p.stats->rho16 : 1.f;
         const float inv_s16 = inv_s / rho16;
-        const float cnmax = __uint_as_float(p.stats->cn_max_bits);
-        (void)inv_s16; (void)cnmax;
+        (void)inv_s16;
         uint32_t ac = 0;
         // row norms of the NEXT row tile are fetched while the current one is scanned
         auto tile_row = [&](int it) { return (int64_t)tile_of(it) * kTcBlockM + q * 32 + lane; };
@@ -609,10 +623,12 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 nn_next = *reinterpret_cast<const float2*>(p.xnorm + 2 * tile_row(it + 1));
             // certified if the two best scores are further apart than twice the score error bound:
             // 3 terms: operand split + accumulator truncation; 1 term: the dropped x_lo.c and x.c_lo too
-            // fp16 accumulators: every MMA instruction rounds the accumulator to fp16 (2^-11 of its magnitude, which
-            // is at most rho16 * (max_k S|c_k|^2 + |X'_i| max_k |C'_k|)), on top of the dropped low-order terms of the
-            // 1-term kernel
-            const float thr = ACC16 ? 2.f * rho16 * (xlo * cmax + xn * clomax + p.gamma16 * (cnmax + xn * cmax))
+            // fp16 accumulators: every MMA instruction of the dot product rounds the accumulator to fp16 (2^-11 of its
+            // magnitude, which is at most rho16 * |X'_i| max_k |C'_k| while only partial dot products have been added),
+            // on top of the dropped low-order terms of the 1-term kernel
+            // (the last MMA step adds the large terms and rounds a small result: its share is the |m1| + |m2| term at
+            // the certification below)
+            const float thr = ACC16 ? 2.f * rho16 * (xlo * cmax + xn * clomax + p.gamma16 * xn * cmax)
                             : (NPASS == 3) ? 2.f * p.gamma * xn * cmax
                                            : 2.f * (xlo * cmax + xn * clomax + p.gamma1 * xn * cmax);
             // 3 terms: offset by ~S*|x|^2 so that scores are S*d >= 0 and the index packing truncates
@@ -863,7 +879,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 if (row_ok) {
                     if ((int)((uint32_t)a1 & kAnchorMask) >= p.K) a1 = 0;
                     p.labels[row] = a1;
-                    const float pack_err = ACC16 ? 0.f : ((SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));
+                    const float pack_err = (ACC16 ? 6.2e-4f : (SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));   // fp16: 1.25 * 2^-11
                     float thr_row = thr;
                     if (NPASS == 1 && !ACC16) {
                         // Tighter bound on the dropped x_lo.(c_k - c_b): |c_k - c_b| <= |x - c_k| + |x - c_b|, and the
@@ -944,6 +960,7 @@ int tc_setup_tensor_maps(kmc_ctx* c) {
                      kTcBlockN / 2));
     KMC_TRY(make_map(fn, &c->tmap_bias_half, c->at<void>(c->off_cbias), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN / 2,
                      kBiasCols, CU_TENSOR_MAP_SWIZZLE_32B));
+    KMC_TRY(make_map(fn, &c->tmap_xext, c->at<void>(c->off_xext), (uint64_t)16, (uint64_t)c->n, kTcBlockM, 16, CU_TENSOR_MAP_SWIZZLE_32B));
     // fp16-accumulator tier: one centroid plane and a bias plane at their own scale
     KMC_TRY(make_map(fn, &c->tmap_c16, c->at<void>(c->off_cplane16), (uint64_t)c->D_pad, (uint64_t)c->K_pad, kTcBlockN));
     KMC_TRY(make_map(fn, &c->tmap_bias16, c->at<void>(c->off_cbias16), (uint64_t)kBiasCols, (uint64_t)c->K_pad, kTcBlockN, kBiasCols,
@@ -1023,10 +1040,18 @@ int launch_compact_worklist(kmc_ctx* c, int32_t* worklist, unsigned long long* a
 //   skip pass:   the 1-term kernel did not run; 3 terms.
 //   probe pass:  the first pass after a skip period keeps its 1-term result unconditionally, so that its refine
 //                measures the overflow share afresh (statistics of 3-term leftovers say nothing about 1-term rows).
-__global__ void tc_gate_kernel(DeviceStats* stats, int ch, unsigned long long rows, int prev_slot) {
+__global__ void tc_gate_kernel(DeviceStats* stats, int ch, unsigned long long rows, int prev_slot, int acc16_policy) {
     unsigned long long* amb = &stats->n_amb[ch];
+    const bool was16 = acc16_policy && stats->acc16_off[ch] == 0u;      // the tier the 1-term pass of this chunk ran with
     if (stats->tc_skip[ch] > 0u) {
-        if (--stats->tc_skip[ch] == 0u) stats->tc_probe[ch] = 1u;
+        if (--stats->tc_skip[ch] == 0u) {
+            stats->tc_probe[ch] = 1u;
+            if (acc16_policy) {          // the probe runs with fp32 accumulators (they certify more: a cheaper probe on
+                stats->acc16_off[ch] = 1u;   // hard data); if it stays with one term, the pass after it tries fp16 again
+                const unsigned int r = stats->rearm[ch] ? stats->rearm[ch] : 2u;
+                stats->t1_ok[ch] = r - 1u;
+            }
+        }
         stats->tc3_flag[ch] = 1u;
         *amb = 0ull;
         return;
@@ -1041,17 +1066,35 @@ __global__ void tc_gate_kernel(DeviceStats* stats, int ch, unsigned long long ro
     unsigned int period = stats->tc_period[ch] ? stats->tc_period[ch] : 1u;
     if (expect_over > 0.018 * (double)rows) {
         stats->tc3_flag[ch] = 1u;
-        stats->tc_skip[ch] = period;
-        stats->tc_period[ch] = period < 16u ? 2u * period : 16u;
         *amb = 0ull;
+        if (was16) {
+            // the fp16 tier left too much to an expensive refine: the fp32-accumulator kernel takes over as first tier
+            // (no skip period: it certifies more rows and gets its own chance at the next pass) until `rearm` passes
+            // in a row stayed with it; `rearm` doubles with every failure of the fp16 tier and restarts at 2 when an
+            // fp16 pass goes through
+            const unsigned int r = stats->rearm[ch] ? stats->rearm[ch] : 2u;
+            stats->acc16_off[ch] = 1u;
+            stats->t1_ok[ch] = 0u;
+            stats->rearm[ch] = r < 32u ? 2u * r : 32u;
+        } else {
+            stats->tc_skip[ch] = period;
+            stats->tc_period[ch] = period < 16u ? 2u * period : 16u;
+            stats->t1_ok[ch] = 0u;
+        }
     } else {
         stats->tc3_flag[ch] = 0u;
         stats->tc_period[ch] = 1u;
+        if (was16) stats->rearm[ch] = 2u;
+        if (acc16_policy && !was16) {       // a pass that stayed with the fp32-accumulator tier: towards re-arming fp16
+            const unsigned int r = stats->rearm[ch] ? stats->rearm[ch] : 2u;
+            if (++stats->t1_ok[ch] >= r) { stats->acc16_off[ch] = 0u; stats->t1_ok[ch] = 0u; }
+        }
     }
 }
 
-int launch_tc_gate(kmc_ctx* c, int ch, int64_t rows, cudaStream_t s) {
-    tc_gate_kernel<<<1, 1, 0, s>>>(c->stats(), ch, (unsigned long long)rows, (int)((c->refine_launches & 1u) ^ 1u));
+int launch_tc_gate(kmc_ctx* c, int ch, int64_t rows, bool acc16_policy, cudaStream_t s) {
+    tc_gate_kernel<<<1, 1, 0, s>>>(c->stats(), ch, (unsigned long long)rows, (int)((c->refine_launches & 1u) ^ 1u),
+                                   acc16_policy ? 1 : 0);
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;
@@ -1063,7 +1106,7 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
     const int grid = p.n_mtiles < c->sm_count ? p.n_mtiles : c->sm_count;
     auto launch = [&](auto kern, uint32_t smem_bytes, const TcParams& pp) -> int {
         KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-        kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, c->tmap_bias, pp);
+        kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c, c->tmap_bias, c->tmap_xext, pp);
         KMC_CUDA(cudaGetLastError());
         c->launches++;
         return 0;
@@ -1085,9 +1128,9 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
         if (c->tc_tile_n == 128) {
             TcParams p4 = pp;
             p4.n_ntiles = pp.n_ntiles * 2;
-            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_quarter, c->tmap_bias_quarter, p4));
+            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_quarter, c->tmap_bias_quarter, c->tmap_xext, p4));
         } else {
-            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_half, c->tmap_bias_half, pp));
+            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c_half, c->tmap_bias_half, c->tmap_xext, pp));
         }
         c->launches++;
         return 0;
@@ -1098,15 +1141,15 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
         // fp16 accumulators (1 term, bias through the MMA at this tier's own scale): its own centroid / bias maps
         auto launch16 = [&](auto kern, uint32_t smem_bytes) -> int {
             KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-            kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c16, c->tmap_bias16, pp);
+            kern<<<grid, threads, smem_bytes, s>>>(c->tmap_xhi, c->tmap_xlo, c->tmap_c16, c->tmap_bias16, c->tmap_xext, pp);
             KMC_CUDA(cudaGetLastError());
             c->launches++;
             return 0;
         };
-        if (p.scores) return launch16(tc_assign_kernel<KC, true, 1, 8, true, 1, 256, true>, TcCfg<KC, 1>::kSmemBytes);
+        if (p.scores) return launch16(tc_assign_kernel<KC, true, 1, 8, true, 1, 256, true>, TcCfg<KC, 1, 1, 256, true>::kSmemBytes);
         if (c->tc_pair && p.n_mtiles >= 2 && p.n_ntiles * KC >= 4) {
             auto kern = tc_assign_kernel<KC, false, 1, 8, true, 2, 256, true>;
-            const uint32_t smem_bytes = TcCfg<KC, 1, 2, 256>::kSmemBytes;
+            const uint32_t smem_bytes = TcCfg<KC, 1, 2, 256, true>::kSmemBytes;
             KMC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
             const int pairs_needed = (p.n_mtiles + 1) / 2, pairs_max = c->sm_count / 2;
             cudaLaunchConfig_t cfg = {};
@@ -1119,11 +1162,11 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
             attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
             cfg.attrs = attr;
             cfg.numAttrs = 1;
-            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c16_half, c->tmap_bias16_half, pp));
+            KMC_CUDA(cudaLaunchKernelEx(&cfg, kern, c->tmap_xhi, c->tmap_xlo, c->tmap_c16_half, c->tmap_bias16_half, c->tmap_xext, pp));
             c->launches++;
             return 0;
         }
-        return launch16(tc_assign_kernel<KC, false, 1, 8, true, 1, 256, true>, TcCfg<KC, 1>::kSmemBytes);
+        return launch16(tc_assign_kernel<KC, false, 1, 8, true, 1, 256, true>, TcCfg<KC, 1, 1, 256, true>::kSmemBytes);
     }
     if (p.scores) return launch(tc_assign_kernel<KC, true, 3, 8, false, 1>, TcCfg<KC, 3>::kSmemBytes, pp);
     if (terms != 1) return launch(tc_assign_kernel<KC, false, 3, 8, false, 1>, TcCfg<KC, 3>::kSmemBytes, pp);
@@ -1147,7 +1190,7 @@ static int launch_tc_kc(kmc_ctx* c, const TcParams& p, int terms, cudaStream_t s
 
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
                      float* scores_out, int64_t r0, int64_t r1, int terms, const unsigned int* gate_flag,
-                     unsigned int gate_want, cudaStream_t s) {
+                     unsigned int gate_want, cudaStream_t s, const unsigned int* gate2, unsigned int gate2_want) {
     if (!c->tmaps_ready) KMC_FAIL(KMC_E_STATE, "tensor maps not built (bind workspace and points first)");
     if (r1 <= r0) return 0;
     if (r0 % kTcBlockM) KMC_FAIL(KMC_E_INVALID, "row chunks of the tensor kernel start at multiples of %d", kTcBlockM);
@@ -1157,6 +1200,8 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.amb_counter = amb_counter;
     p.gate_flag = gate_flag;
     p.gate_want = gate_want;
+    p.gate2 = gate2;
+    p.gate2_want = gate2_want;
     p.K = (int)c->K;
     p.K_pad = (int)c->K_pad;
     p.n_mtiles = (int)((r1 - r0 + kTcBlockM - 1) / kTcBlockM);
@@ -1172,7 +1217,7 @@ int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigne
     p.gamma1 = (float)(1.25 * ((double)(c->D_pad / 16) + 6.0) / 8388608.0);
     // one rounding to fp16 (2^-11 of the accumulator, round to nearest) per MMA instruction of a tile, 25 % head-room;
     // measured on the GPU (tools/check_acc16.py): the largest score error is 0.47 of this bound
-    p.gamma16 = (float)(1.25 * ((double)(c->D_pad / 16) + 1.0) / 2048.0);
+    p.gamma16 = (float)(1.25 * (double)(c->D_pad / 16) / 2048.0);
     p.pack_mask = 0xFFFFFF80u;
     p.blk_mask = ~(uint32_t)(kEpiBlocksPerHalf - 1);
     p.x = c->points;

@@ -61,6 +61,7 @@ static void layout_workspace(kmc_ctx* c) {
         c->off_ccdist = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;   // pruning table of the refine pass
         if (c->K <= 8192) c->off_overflow = take(c->n * 4);            // rows whose refine walk hit its cap
         c->off_nbr = (c->K <= 8192) ? take(c->K * c->K * 4) : -1;      // ... sorted nearest-first per centroid
+        c->off_xext = take(c->n * 16 * 2);                 // per row: constants + fp16 pieces of |X'|^2 (fp16-accumulator tier)
         c->off_xhi = take(c->n * c->D_pad * 2);
         c->off_xlo = take(c->n * c->D_pad * 2);
     }
@@ -116,13 +117,24 @@ static int refine_worklist(kmc_ctx* c, int32_t* labels, const int32_t* worklist,
 static int tc_pass(kmc_ctx* c, int32_t* labels, int64_t r0, int64_t r1, int ch, cudaStream_t s) {
     unsigned long long* cnt = &c->stats()->n_amb[ch];
     const bool adaptive = c->tc_terms == 0 && c->off_nbr >= 0;
-    const int first_terms = c->tc_terms ? c->tc_terms : (adaptive ? 1 : 3);
+    // adaptive: the cheapest tier first -- fp16 accumulators where a K sweep has at least two accumulator tiles (with
+    // one tile per row tile, config 3, its heavier end-of-tile work cancels the gain: 0.832 against 0.836 ms per
+    // iteration), unless the device has switched that tier off for the chunk (DeviceStats::acc16_off), in which case
+    // the fp32-accumulator 1-term kernel enqueued right behind it runs instead
+    const bool acc16_policy = adaptive && c->tc_acc16 && c->K_pad >= 2 * kTcBlockN;
     const unsigned int* skip = adaptive ? &c->stats()->tc_skip[ch] : nullptr;
-    KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, first_terms, skip, 0u, s));
+    if (acc16_policy) {
+        const unsigned int* off = &c->stats()->acc16_off[ch];
+        KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, 16, skip, 0u, s, off, 0u));
+        KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, 1, skip, 0u, s, off, 1u));
+    } else {
+        const int first_terms = c->tc_terms ? c->tc_terms : (adaptive ? 1 : 3);
+        KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, first_terms, skip, 0u, s));
+    }
     KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, skip, 0u, s));
     if (adaptive) {
         unsigned int* flag = &c->stats()->tc3_flag[ch];
-        KMC_TRY(launch_tc_gate(c, ch, r1 - r0, s));
+        KMC_TRY(launch_tc_gate(c, ch, r1 - r0, acc16_policy, s));
         KMC_TRY(launch_tc_assign(c, labels, c->perm() + r0, cnt, nullptr, r0, r1, 3, flag, 1u, s));
         KMC_TRY(launch_compact_worklist(c, c->perm() + r0, cnt, r0, r1, flag, 1u, s));
     }
@@ -725,6 +737,9 @@ int kmc_set_param(kmc_ctx* c, int param, double value) {
             return 0;
         case KMC_PARAM_TC_PAIR:
             c->tc_pair = value != 0.0;
+            return 0;
+        case KMC_PARAM_TC_ACC16:
+            c->tc_acc16 = value != 0.0;
             return 0;
         case KMC_PARAM_INCREMENTAL:
             c->delta_enabled = value != 0.0;

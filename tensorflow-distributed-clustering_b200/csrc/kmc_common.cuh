@@ -66,6 +66,12 @@ struct DeviceStats {
     unsigned int tc_skip[kMaxChunks];       // passes for which the chunk goes straight to the 3-term kernel
     unsigned int tc_period[kMaxChunks];     // length of the next skip period (1, 2, 4 ... 16)
     unsigned int tc_probe[kMaxChunks];      // the next pass keeps its 1-term result whatever the statistics say
+    // fp16-accumulator tier of the adaptive policy: 1 = off for this chunk (its wider certification margin made the
+    // gate fall back to 3 terms; the fp32-accumulator 1-term kernel, which certifies more rows, is the first tier
+    // until `t1_ok` passes in a row stayed with it -- `rearm` of them, doubling with every failure of the fp16 tier)
+    unsigned int acc16_off[kMaxChunks];
+    unsigned int t1_ok[kMaxChunks];
+    unsigned int rearm[kMaxChunks];
     // exact distances evaluated / rows handled by the last two refine launches (slot = launch parity): the next
     // launch reads the previous slot to pick the kernel that fits the walk lengths (see refine.cu)
     unsigned long long walk[2][4];          // [slot]: distances evaluated, rows refined, rows handed to the tile kernel, -
@@ -91,7 +97,7 @@ struct kmc_ctx {
     int64_t D_pad = 0, K_pad = 0;
     double tc_gamma = 0.0;
     int tc_terms = 0;                   // KMC_PARAM_TC_TERMS: 0 = adaptive, 1 or 3 = fixed, 16 = 1 term with fp16 accumulators
-    bool tc_acc16 = false;              // KMC_PARAM_TC_ACC16: adaptive policy starts with the fp16-accumulator tier
+    bool tc_acc16 = true;               // KMC_PARAM_TC_ACC16: the adaptive policy starts with the fp16-accumulator tier
     int n_chunks = 1;                   // row chunks per accumulate pass (tensor path, large shards)
     cudaStream_t side_stream = nullptr; // refine + accumulation of chunk c run here while chunk c+1 is assigned
     cudaEvent_t chunk_done[kmc::kMaxChunks] = {};
@@ -109,7 +115,7 @@ struct kmc_ctx {
     int64_t off_centroids = 0, off_partials = 0, off_stats = 0, off_labels = 0, off_labels2 = 0, off_perm = 0,
             off_changed = 0, off_running = 0, off_overflow = 0,
             off_sort = 0, sort_stride = 0, sort_cursor = 0, sort_offsets = 0, sort_segoff = 0,
-            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0, off_ambmask = 0, off_cplane16 = 0, off_cbias16 = 0,
+            off_xhi = 0, off_xlo = 0, off_xnorm = 0, off_cplanes = 0, off_cnorm = 0, off_cbias = 0, off_ambmask = 0, off_cplane16 = 0, off_cbias16 = 0, off_xext = 0,
             off_ccdist = -1, off_nbr = -1;
     const float* points = nullptr;
     // incremental accumulation: two label buffers (this pass / previous pass), running fp64 sums and counts
@@ -130,7 +136,7 @@ struct kmc_ctx {
     alignas(64) CUtensorMap tmap_bias;
     alignas(64) CUtensorMap tmap_c_half;      // 128-row boxes: the halves of a centroid stage a CTA pair loads
     alignas(64) CUtensorMap tmap_bias_half;
-    alignas(64) CUtensorMap tmap_c16, tmap_bias16, tmap_c16_half, tmap_bias16_half;   // fp16-accumulator tier
+    alignas(64) CUtensorMap tmap_c16, tmap_bias16, tmap_c16_half, tmap_bias16_half, tmap_xext;   // fp16-accumulator tier
     alignas(64) CUtensorMap tmap_c_quarter;   // 64-row boxes: a CTA's half of a 128-centroid stage
     alignas(64) CUtensorMap tmap_bias_quarter;
     int tc_tile_n = 256;                      // KMC_PARAM_TC_TILE_N: centroids per accumulator tile of the pair kernel
@@ -194,13 +200,14 @@ bool tc_path_supported(int64_t K, int64_t D);
 int tc_setup_tensor_maps(kmc_ctx* c);
 // rows [r0, r1) (r0 a multiple of 128); uncertified rows are appended to `worklist`, counted in `amb_counter`
 // `terms` = 1 or 3 MMA terms; `gate_flag` (may be null): the launch is a no-op unless *gate_flag == gate_want
+// `gate2` (may be null): a second device flag of the same kind
 int launch_tc_assign(kmc_ctx* c, int32_t* labels_out, int32_t* worklist, unsigned long long* amb_counter,
                      float* scores_out, int64_t r0, int64_t r1, int terms, const unsigned int* gate_flag,
-                     unsigned int gate_want, cudaStream_t s);
+                     unsigned int gate_want, cudaStream_t s, const unsigned int* gate2 = nullptr, unsigned int gate2_want = 0u);
 // rows [r0, r1) (r0 a multiple of 32): masks of uncertified rows -> worklist, their number added to *amb_counter
 int launch_compact_worklist(kmc_ctx* c, int32_t* worklist, unsigned long long* amb_counter, int64_t r0, int64_t r1,
                             const unsigned int* gate_flag, unsigned int gate_want, cudaStream_t s);
-int launch_tc_gate(kmc_ctx* c, int chunk, int64_t rows, cudaStream_t s);
+int launch_tc_gate(kmc_ctx* c, int chunk, int64_t rows, bool acc16_policy, cudaStream_t s);
 // refine.cu
 int launch_ccdist(kmc_ctx* c, cudaStream_t s);
 int launch_refine(kmc_ctx* c, int32_t* labels, const int32_t* worklist, const unsigned long long* n_work_dev,

@@ -103,8 +103,8 @@ int launch_absmax(kmc_ctx* c, const float* x, int64_t count, unsigned int* out_b
 __global__ void __launch_bounds__(256) split_points_kernel(const float* __restrict__ x, int64_t row0, int64_t n, int D,
                                                            int D_pad, __half* __restrict__ xhi,
                                                            __half* __restrict__ xlo,
-                                                           float* __restrict__ xnorm, DeviceStats* stats,
-                                                           int keep_scale) {
+                                                           float* __restrict__ xnorm, __half* __restrict__ xext,
+                                                           DeviceStats* stats, int keep_scale) {
     const float sigma = keep_scale ? stats->sigma_x : scale_from_absmax(__uint_as_float(stats->x_absmax_bits));
     if (!keep_scale && blockIdx.x == 0 && threadIdx.x == 0) stats->sigma_x = sigma;
     const int lane = threadIdx.x & 31;
@@ -129,6 +129,26 @@ __global__ void __launch_bounds__(256) split_points_kernel(const float* __restri
         if (lane == 0) {
             xnorm[2 * row] = sqrtf(ss) * 1.001f;
             xnorm[2 * row + 1] = sqrtf(ss_lo) * 1.001f;
+            // fp16-accumulator tier: the row's 16-column extension of the A operand for the bias MMA step --
+            // [a_0..a_5 | r_0..r_5 | 0 0 0 0], a = kBiasConst (they meet the fp16 pieces of S|c_k|^2 in the centroid's
+            // bias row) and sum_i a_i r_i = |X'_row|^2 (it meets kappa * a_i there: the MMA adds S|x|^2 to every score
+            // of the row, so the scores of near centroids are small numbers with fine fp16 spacing)
+            __half e[16];
+            double r = (double)ss;
+#pragma unroll
+            for (int i = 0; i < kBiasPieces; ++i) {
+                e[i] = __float2half_rn(kBiasConst[i]);
+                float q = (float)(r / (double)kBiasConst[i]);
+                q = fminf(fmaxf(q, -65504.f), 65504.f);
+                const __half h = __float2half_rn(q);
+                e[kBiasPieces + i] = h;
+                r -= (double)kBiasConst[i] * (double)__half2float(h);
+            }
+#pragma unroll
+            for (int i = 2 * kBiasPieces; i < 16; ++i) e[i] = __float2half_rn(0.f);
+            uint4* dst = reinterpret_cast<uint4*>(xext + row * 16);
+            dst[0] = *reinterpret_cast<const uint4*>(e);
+            dst[1] = *reinterpret_cast<const uint4*>(e + 8);
         }
     }
 }
@@ -142,7 +162,8 @@ int launch_split_points_range(kmc_ctx* c, int64_t r0, int64_t r1, bool keep_scal
     if (blocks < 1) blocks = 1;
     split_points_kernel<<<(unsigned)blocks, 256, 0, s>>>(c->points, r0, r1, (int)c->D, (int)c->D_pad,
                                                          c->at<__half>(c->off_xhi), c->at<__half>(c->off_xlo),
-                                                         c->at<float>(c->off_xnorm), c->stats(), keep_scale ? 1 : 0);
+                                                         c->at<float>(c->off_xnorm), c->at<__half>(c->off_xext), c->stats(),
+                                                         keep_scale ? 1 : 0);
     KMC_CUDA(cudaGetLastError());
     c->launches++;
     return 0;

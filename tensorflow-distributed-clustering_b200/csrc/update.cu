@@ -100,10 +100,10 @@ int launch_centroid_absmax(kmc_ctx* c, cudaStream_t s) {
 // cn'[k] = sigma_x * sigma_c * |c_k|^2 (3e38 for padding rows and NaN centroids, so they never
 // win), plus max_k |C'_k| for the refine threshold.
 // fp16-accumulator tier: a second, smaller centroid scale sigma_c16 = rho16 * sigma_c (power of two) such that no
-// partial sum of a score can leave the fp16 range: |S16 (|c_k|^2 - 2 x_i.c_k)| <= S16 * D * (cabs^2 + 2 xabs cabs)
-// < 24000 with S16 = sigma_x * sigma_c16 (the bound uses |v| <= sqrt(D) * absmax for rows and centroids alike).
+// partial sum of a score can leave the fp16 range: S16 |x_i - c_k|^2 and every part of it is at most
+// S16 * D * (xabs + cabs)^2 < 24000 with S16 = sigma_x * sigma_c16 (|v| <= sqrt(D) * absmax for rows and centroids).
 __device__ __forceinline__ float rho16_for(float sigma_x, float sigma_c, float xabs, float cabs, int D) {
-    const float bound = sigma_x * sigma_c * (float)D * (cabs * cabs + 2.f * xabs * cabs);
+    const float bound = sigma_x * sigma_c * (float)D * (xabs + cabs) * (xabs + cabs);
     if (!(bound > 0.f) || !(bound < 3.0e38f)) return 1.f;
     int e;
     frexpf(bound / 24000.f, &e);          // bound / 24000 = f * 2^e, f in [0.5, 1)  ->  rho = 2^-e keeps bound * rho < 24000
@@ -186,7 +186,12 @@ __global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __rest
                 }
             }
             __syncwarp();
-            if (lane >= kBiasPieces && lane < kBiasCols) cbias16[(int64_t)k * kBiasCols + lane] = __float2half_rn(0.f);
+            // columns 6..11: kappa * a_i, the partners of the row's pieces of |X'|^2 (kappa = S16 / sigma_x^2)
+            if (lane >= kBiasPieces && lane < kBiasCols) {
+                float q = 0.f;
+                if (lane < 2 * kBiasPieces) q = fminf(kBiasConst[lane - kBiasPieces] * (rho16 * sigma_c / sigma_x), 65504.f);
+                cbias16[(int64_t)k * kBiasCols + lane] = __float2half_rn(q);
+            }
         }
         if (lane == 0) {
             cnorm[k] = dead ? 3.0e38f : cn;

@@ -105,17 +105,17 @@ def test_random_shapes_each_path(n, d, k, path, pkg, cuda_device):
     assert stats["path"] == path
 
 
-@pytest.mark.parametrize("terms", [1, 3])
+@pytest.mark.parametrize("terms", [1, 3, 16])
 @pytest.mark.parametrize("n,d,k", [(6000, 128, 1024), (5000, 64, 300), (3000, 256, 512), (2500, 32, 256)])
 def test_tensor_path_with_one_and_three_mma_terms(n, d, k, terms, pkg, cuda_device):
-    """Both precisions of the tensor kernel must end in the same exact labels: with one MMA term many
-    more rows go through the exact refine kernel, with three almost none."""
+    """Every precision tier of the tensor kernel must end in the same exact labels: with one MMA term (fp32 or,
+    terms = 16, fp16 accumulators) many more rows go through the exact refine kernel, with three almost none."""
     X, _ = pkg.datagen.blobs_numpy(n, d, max(2, k // 4), seed=n + d + k)      # several centroids per blob
     stats = _check_iterations(pkg, X, X[:k].copy(), 2, cuda_device, path="tc", form="gemm", tc_terms=terms)
     assert stats["path"] == "tc"
 
 
-@pytest.mark.parametrize("chunks,terms", [(4, 1), (3, 3), (2, 0)])
+@pytest.mark.parametrize("chunks,terms", [(4, 1), (3, 3), (2, 0), (3, 16)])
 def test_chunk_pipelined_accumulate(chunks, terms, pkg, cuda_device):
     """KMC_PARAM_CHUNKS > 1: the shard is assigned chunk by chunk while the finished chunk is refined on a
     second stream; check every iteration against the oracle, with and without the incremental accumulation."""
@@ -223,7 +223,7 @@ def test_host_staging_fp64_fp32_and_batches(pkg, cuda_device):
             s.close()
 
 
-@pytest.mark.parametrize("terms", [1, 3])
+@pytest.mark.parametrize("terms", [1, 3, 16])
 def test_well_separated_rows_are_certified_by_the_tensor_kernel(terms, pkg, cuda_device):
     """Guards the epilogue's best / second-best bookkeeping: on blobs with one centroid each nearly every row
     must be certified by the tensor kernel itself (a wrong second-best would flood or starve the refine)."""
@@ -639,3 +639,44 @@ def test_fused_small_path_iterate_equals_accumulate_update(n, d, k, iters, pkg, 
     assert oracle.rel_err(a.get_centroids(), b.get_centroids()) <= 1e-6
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("n,d,k", [(4096, 128, 1024), (6000, 64, 2048), (3000, 96, 300)])
+def test_fp16_accumulator_scores_stay_inside_the_bound_the_kernel_certifies_with(n, d, k, pkg, cuda_device):
+    """The fp16-accumulator tier (KMC_PARAM_TC_TERMS = 16) returns S16 |x - c|^2 through packed TMEM reads: the raw
+    scores against float64, measured against the accumulation part of the kernel's error bound (one fp16 rounding
+    per MMA instruction of the dot product plus the rounding of the final value)."""
+    X, _ = pkg.datagen.blobs_numpy(n, d, max(2, k // 2), seed=7)
+    C0 = X[:k].copy()
+    s = _shard(pkg, X, k, cuda_device, path="tc")
+    s.set_centroids(C0)
+    s.set_param(pkg._lib.KMC_PARAM_TC_TERMS, 16)
+    S = s.debug_tc_scores().double().cpu().numpy()
+    s.close()
+    X64, C64 = X.astype(np.float64), C0.astype(np.float64)
+    T = (X64 * X64).sum(1)[:, None] + (C64 * C64).sum(1)[None, :] - 2.0 * X64 @ C64.T
+    xn, cn = np.sqrt((X64 * X64).sum(1)), np.sqrt((C64 * C64).sum(1))
+    steps = (-(-d // 64) * 64) // 16
+    bound = 1.25 * steps / 2048.0 * 2.0 * xn[:, None] * cn.max() + 1.25 / 2048.0 * np.abs(T)
+    assert (np.abs(S - T) / bound).max() < 0.8
+
+
+def test_fp16_accumulator_tier_with_many_equal_scores(pkg, cuda_device):
+    """Integer-valued rows and centroids make many fp16 scores of a row EQUAL (exact ties of the best value in two,
+    three and more cells of the epilogue's partition): such rows must reach the refine with a usable anchor and
+    end with the exact label (lowest index among equal distances)."""
+    rng = np.random.default_rng(5)
+    n, d, k = 20000, 64, 1024
+    X = rng.integers(-3, 4, size=(n, d)).astype(np.float32)
+    C0 = np.unique(X[:4 * k], axis=0)[:k].copy()
+    assert C0.shape[0] == k
+    C0[1::7] = C0[0::7][: len(C0[1::7])]                       # duplicated centroids: exact ties everywhere
+    s = _shard(pkg, X, k, cuda_device, path="tc")
+    s.set_centroids(C0)
+    s.set_param(pkg._lib.KMC_PARAM_TC_TERMS, 16)
+    lab = s.assign().cpu().numpy()
+    st = s.stats()
+    s.close()
+    ref, d1, d2 = oracle.assign(X, C0)
+    assert np.array_equal(lab, ref)                             # integer data: distances are exact, ties -> lowest index
+    assert st["ambiguous"] > 0

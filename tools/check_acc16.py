@@ -24,14 +24,14 @@ for (n, d, k) in [(4096, 128, 1024), (8192, 64, 4096), (5000, 32, 256), (3000, 9
     shard.bind_points(torch.from_numpy(X).to(dev))
     shard.set_centroids(C0)
     shard.set_param(L.KMC_PARAM_TC_TERMS, 16)
-    S = shard.debug_tc_scores().double().cpu().numpy()                       # |c|^2 - 2 x.c, as the tier sees it
+    S = shard.debug_tc_scores().double().cpu().numpy()                       # |x - c|^2, as the tier sees it
     X64, C64 = X.astype(np.float64), C0.astype(np.float64)
-    T = (C64 * C64).sum(1)[None, :] - 2.0 * X64 @ C64.T
+    T = (X64 * X64).sum(1)[:, None] + (C64 * C64).sum(1)[None, :] - 2.0 * X64 @ C64.T       # the tier adds |x|^2 through the MMA
     err = np.abs(S - T)
     xn = np.sqrt((X64 * X64).sum(1))
     cn = np.sqrt((C64 * C64).sum(1))
-    steps = (-(-d // 64) * 64) // 16 + 1
-    bound = 1.25 * steps / 2048.0 * ((cn * cn).max() + xn[:, None] * cn.max())     # the accumulation part of the kernel's bound
+    steps = (-(-d // 64) * 64) // 16
+    bound = 1.25 * steps / 2048.0 * 2.0 * xn[:, None] * cn.max() + 1.25 / 2048.0 * np.abs(T)     # the accumulation part of the kernel's bound
     ratio = (err / bound).max()
     print(f"n={n} D={d} K={k}: max |score error| {err.max():.4g} (scores up to {np.abs(T).max():.4g}), "
           f"max error / accumulation bound {ratio:.3f}, mean {np.mean(err / bound):.4f}")
