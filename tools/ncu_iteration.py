@@ -19,7 +19,7 @@ for r in rows:
         order.append(lid)
     launches[lid][r[12]] = float(r[14].replace(",", "")) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "byte": 1e-9, "Kbyte": 1e-6,
                                                              "Mbyte": 1e-3, "Gbyte": 1.0}.get(r[13], 1.0)
-ours = [i for i in order if "kmc::" in launches[i]["name"]]
+ours = [i for i in order if "kmc::" in launches[i]["name"]] or list(order)      # (with ncu -k the names come without the namespace)
 starts = [i for i in ours if first in launches[i]["name"]]
 if not starts:
     raise SystemExit(f"no launch of {first}")
