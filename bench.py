@@ -451,7 +451,7 @@ def main():
                    "accumulation": "incremental: running fp64 sums updated with the rows whose label changed; a device-side "
                                    "gate takes the full pass when more than a quarter of the rows moved (every N*K distance is "
                                    "evaluated either way)" if stats["path"] != "small" else "fused into the assignment kernel",
-                   "tensor_terms": "adaptive (1 fp16 MMA term + exact refine; device-side fallback to the 3-term split where the refine walks are long and >3% of a chunk is uncertified)"
+                   "tensor_terms": "adaptive: 1 fp16 MMA term (fp16 accumulators for K > 256, else fp32) + exact refine of the uncertified rows; device-side fall-back to fp32 accumulators / the 3-term split where the refine would cost more"
                    if stats["path"] == "tc" else None},
         "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
     }
