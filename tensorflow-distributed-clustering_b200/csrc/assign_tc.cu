@@ -282,9 +282,6 @@ __device__ __forceinline__ void epi_chunk_part(const uint32_t (&r)[32], const fl
             ga[g] = fmin3(ga[g], v[g], v[16 + g]);
         }
     }
-#ifdef KMC_ABL_NO_B
-    return;
-#endif
     // partition B
     float bm[32 / kEpiG];
 #pragma unroll
@@ -357,11 +354,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
     constexpr int NB = Cfg::kTBufs;              // accumulator tiles in TMEM (2 or 4)
     // kind::f16, fp16 x fp16 -> fp32, A and B K-major, N = BN, M = 128 (one CTA) or 256 (the MMA a CTA pair shares)
     // ... accumulator (bits 4-5): 1 = fp32, 0 = fp16 (ACC16)
-#ifdef KMC_ABL_F32DESC
-    constexpr uint32_t kAccFmt = 1u;
-#else
     constexpr uint32_t kAccFmt = ACC16 ? 0u : 1u;
-#endif
     constexpr uint32_t kInstrDescT = (kAccFmt << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((NCTA * kTcBlockM) >> 4) << 24);
     static_assert(!ACC16 || (NPASS == 1 && AUG), "fp16 accumulators exist for the 1-term kernel with the bias MMA");
     static_assert(NCTA == 1 || (NPASS == 1 && AUG && !SCORES), "the CTA-pair kernel exists for the 1-term AUG variant");
@@ -673,9 +666,6 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 const float e_in = te.m1, o_in = to.m1, b_in = tb.m1;
                 const int kbase = nt * BN + half * kCols;
                 uint32_t ra[32], rb[32];
-#ifdef KMC_ABL_NO_EPI
-                if (p.n < 0) {
-#endif
                 if constexpr (ACC16) {
                     static_assert(!ACC16 || kCols == 128, "two packed loads of 64 columns per warp and tile");
                     tmem_ld_32x64_pack16(taddr, ra);
@@ -723,9 +713,6 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                                                          ga, tb);
                 }
                 }
-#ifdef KMC_ABL_NO_EPI
-                }
-#endif
                 tc_fence_before_sync();
                 __syncwarp();
                 if (threadIdx.x == 128) KMC_TRACE_AT(ac, 3);
@@ -895,9 +882,6 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                         if (r2 > rho) thr_row = fminf(thr, tight);                // (monotonicity needs r > rho / 2)
                     }
                     amb = p.worklist && !((m2 - m1) > thr_row + pack_err);        // NaNs count as uncertified
-#ifdef KMC_ABL_NO_B
-                    amb = false;
-#endif
                 }
                 // uncertified rows: one 32-bit mask per warp and row tile, no atomic and no dependent store on
                 // this path (a returning atomic here costs ~800 cycles per row tile in warps that hold two of the
