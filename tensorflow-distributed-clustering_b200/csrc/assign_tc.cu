@@ -1031,9 +1031,8 @@ __global__ void tc_gate_kernel(DeviceStats* stats, int ch, unsigned long long ro
         if (--stats->tc_skip[ch] == 0u) {
             stats->tc_probe[ch] = 1u;
             if (acc16_policy) {          // the probe runs with fp32 accumulators (they certify more: a cheaper probe on
-                stats->acc16_off[ch] = 1u;   // hard data); if it stays with one term, the pass after it tries fp16 again
-                const unsigned int r = stats->rearm[ch] ? stats->rearm[ch] : 2u;
-                stats->t1_ok[ch] = r - 1u;
+                stats->acc16_off[ch] = 1u;   // hard data); if the pass after it stays with one term, fp16 is tried again
+                stats->t1_ok[ch] = 1u;
             }
         }
         stats->tc3_flag[ch] = 1u;
@@ -1053,25 +1052,24 @@ __global__ void tc_gate_kernel(DeviceStats* stats, int ch, unsigned long long ro
         *amb = 0ull;
         if (was16) {
             // the fp16 tier left too much to an expensive refine: the fp32-accumulator kernel takes over as first tier
-            // (no skip period: it certifies more rows and gets its own chance at the next pass) until `rearm` passes
-            // in a row stayed with it; `rearm` doubles with every failure of the fp16 tier and restarts at 2 when an
-            // fp16 pass goes through
+            // (no skip period: it certifies more rows and gets its own chance at the next pass) until `t1_ok` more
+            // passes stayed with it; that count (`rearm`) doubles with every failure of the fp16 tier, up to 32, and
+            // restarts at 2 when an fp16 pass goes through
             const unsigned int r = stats->rearm[ch] ? stats->rearm[ch] : 2u;
             stats->acc16_off[ch] = 1u;
-            stats->t1_ok[ch] = 0u;
+            stats->t1_ok[ch] = r;
             stats->rearm[ch] = r < 32u ? 2u * r : 32u;
         } else {
             stats->tc_skip[ch] = period;
             stats->tc_period[ch] = period < 16u ? 2u * period : 16u;
-            stats->t1_ok[ch] = 0u;
         }
     } else {
         stats->tc3_flag[ch] = 0u;
         stats->tc_period[ch] = 1u;
         if (was16) stats->rearm[ch] = 2u;
         if (acc16_policy && !was16) {       // a pass that stayed with the fp32-accumulator tier: towards re-arming fp16
-            const unsigned int r = stats->rearm[ch] ? stats->rearm[ch] : 2u;
-            if (++stats->t1_ok[ch] >= r) { stats->acc16_off[ch] = 0u; stats->t1_ok[ch] = 0u; }
+            if (stats->t1_ok[ch] <= 1u) { stats->acc16_off[ch] = 0u; stats->t1_ok[ch] = 0u; }
+            else --stats->t1_ok[ch];
         }
     }
 }

@@ -68,7 +68,7 @@ struct DeviceStats {
     unsigned int tc_probe[kMaxChunks];      // the next pass keeps its 1-term result whatever the statistics say
     // fp16-accumulator tier of the adaptive policy: 1 = off for this chunk (its wider certification margin made the
     // gate fall back to 3 terms; the fp32-accumulator 1-term kernel, which certifies more rows, is the first tier
-    // until `t1_ok` passes in a row stayed with it -- `rearm` of them, doubling with every failure of the fp16 tier)
+    // until `t1_ok` more passes stayed with it -- `rearm` of them at first, doubling with every failure of the fp16 tier)
     unsigned int acc16_off[kMaxChunks];
     unsigned int t1_ok[kMaxChunks];
     unsigned int rearm[kMaxChunks];

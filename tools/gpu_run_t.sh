@@ -16,7 +16,7 @@ PY
 }
 timeout 900 python bench.py --no-e2e --no-cpu-baseline > gpurun_out/t_bench_c4.json 2> gpurun_out/t_bench_c4.err; line gpurun_out/t_bench_c4.json
 timeout 900 python bench.py --config c5 --rows 125000000 --steps 5 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/t_bench_c5slice.json 2> gpurun_out/t_bench_c5slice.err; line gpurun_out/t_bench_c5slice.json
-for v in "--data uniform" "--sigma 4"; do
+for v in "--data uniform"; do
   tag=$(echo $v | tr -d ' -' )
   timeout 900 python bench.py --steps 10 --warmup 3 --no-e2e --no-cpu-baseline $v > gpurun_out/t_bench_c4_$tag.json 2> gpurun_out/t_bench_c4_$tag.err
   line gpurun_out/t_bench_c4_$tag.json
