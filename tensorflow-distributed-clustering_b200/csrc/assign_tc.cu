@@ -865,6 +865,7 @@ tc_assign_kernel(const __grid_constant__ CUtensorMap tm_xhi, const __grid_consta
                 bool amb = false;
                 if (row_ok) {
                     if ((int)((uint32_t)a1 & kAnchorMask) >= p.K) a1 = 0;
+                    if (!p.worklist) a1 = (int)((uint32_t)a1 & kAnchorMask);      // no refine behind this launch: plain labels
                     p.labels[row] = a1;
                     const float pack_err = (ACC16 ? 6.2e-4f : (SCORES || kOldEpi) ? kPackRel : kBlkPackRel) * (fabsf(m1) + fabsf(m2));   // fp16: 1.25 * 2^-11
                     float thr_row = thr;
