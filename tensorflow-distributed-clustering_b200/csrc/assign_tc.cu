@@ -9,7 +9,9 @@
 // planes at one scale (v = hi + lo, |lo| <= 2^-11 |hi|).  Three MMAs (hi*hi + lo*hi + hi*lo, NPASS = 3)
 // accumulate the fp32-accurate score BASELINE.json asks for (kind::f16 instead of kind::tf32: same ~2^-22
 // operand accuracy, half the tensor time per term, and the two planes are exactly the 4 bytes/element of
-// the fp32 point).  The default (NPASS = 1) issues hi*hi only and bounds the dropped terms per row.
+// the fp32 point).  The default (NPASS = 1) issues hi*hi only and bounds the dropped terms per row; for K > 256 its
+// first tier accumulates in fp16 (ACC16: packed TMEM reads and a half2 epilogue, half the ALU work per score; the
+// bias MMA step then also adds S|x_i|^2, so the accumulator ends at S|x_i - c_k|^2 where fp16 spacing is fine).
 //
 // The epilogue finds, per row, the exact best and second-best score of the accumulator values (partition
 // epilogue below: 1.44 min/max/logic instructions per score).  Rows whose two best scores are closer than a
@@ -22,6 +24,7 @@
 //   warp 0  TMA producer      warp 1  MMA issuer (one thread)     warp 2  TMEM alloc/dealloc
 //   warps 4-11  epilogue: tcgen05.ld 32 lanes x 32 columns (two warps per TMEM lane quarter, each scanning
 //   one 128-column half of the accumulator tile; they meet once per row tile on one-way named barriers)
+// (cta_group::2: two CTAs on the SMs of one TPC share every MMA, M = 256, each staging half of every centroid stage.)
 // Pipelines: A tiles (points, resident for the whole K sweep, double buffered when they fit), B stages
 // (256 centroids x 64 columns, 3-4 deep ring; with AUG one 8 KB bias-plane stage per tile adds S*|c_k|^2
 // through an extra K=16 MMA), two TMEM accumulators of 256 columns.
