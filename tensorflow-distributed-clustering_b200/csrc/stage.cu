@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(256) split_points_kernel(const float* __restri
             // [a_0..a_5 | r_0..r_5 | 0 0 0 0], a = kBiasConst (they meet the fp16 pieces of S|c_k|^2 in the centroid's
             // bias row) and sum_i a_i r_i = |X'_row|^2 (it meets kappa * a_i there: the MMA adds S|x|^2 to every score
             // of the row, so the scores of near centroids are small numbers with fine fp16 spacing)
-            __half e[16];
+            __align__(16) __half e[16];
             double r = (double)ss;
 #pragma unroll
             for (int i = 0; i < kBiasPieces; ++i) {
