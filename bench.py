@@ -651,7 +651,7 @@ def run_e2e_pageable_f64(pkg, host_f32, C0, D, K, steps, dev):
     """The drop-in's real input (reference :303, notebooks/Testing Images.ipynb:329): an ordinary PAGEABLE float64
     NumPy array handed to `distribuited_k_means`.  The array is a float64 copy of a bounded number of rows of the
     same workload (a float64 copy of all 100M rows of config 4 would need 102 GB of host memory); the timed
-    region is the whole call: host threads copy into pinned chunks, H2D, fp64 -> fp32 on the device, plane split,
+    region is the whole call: host threads convert to fp32 into pinned chunks, H2D, plane split,
     `steps` iterations, centroids and int64 labels back."""
     import psutil
     import torch
@@ -664,7 +664,8 @@ def run_e2e_pageable_f64(pkg, host_f32, C0, D, K, steps, dev):
     res = pkg.distribuited_k_means(X64, K, [f"/device:GPU:{dev.index}"], C0.astype(np.float64), steps)
     dt = time.perf_counter() - t0
     return {"value": rows * res["n_iter"] / dt, "unit": UNIT, "rows": rows, "iterations": res["n_iter"], "seconds": dt,
-            "h2d_bytes_per_step": int(rows * D * 8 / max(steps, 1)),
+            "h2d_bytes_per_step": int(rows * D * 4 / max(steps, 1)),     # the host threads convert to fp32 on their way into the pinned chunks
+            "host_bytes_read_per_step": int(rows * D * 8 / max(steps, 1)),
             "d2h_bytes_per_step": int((K * D * 4 + rows * 8) / max(steps, 1)),
             "initialization_time": res["initialization_time"], "computation_time": res["computation_time"],
             "input": "pageable float64 NumPy array (the reference's callers' dtype)"}

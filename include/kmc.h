@@ -125,8 +125,9 @@ int kmc_accumulate_rows(kmc_ctx* ctx, int64_t r0, int64_t r1, void* stream);
 
 /*
  * Pinned, double-buffered host->device staging of rows [row0, row0+n_rows) of a host array
- * (fp32 or fp64, row-major [*, D]) into `dev_dst` (fp32 [n_rows, D]); fp64 is converted on the
- * device.  Replaces the feed of `all_data` + `tf.split` + per-GPU variable init (:196-197, :217,
+ * (fp32 or fp64, row-major [*, D]) into `dev_dst` (fp32 [n_rows, D]); pageable fp64 rows are converted
+ * to fp32 by the host threads that copy them into the pinned chunks, pinned fp64 rows on the device
+ * (same rounding either way).  Replaces the feed of `all_data` + `tf.split` + per-GPU variable init (:196-197, :217,
  * :273).  `dev_dst` is any fp32 device buffer (normally a slice of the points buffer).
  * Returns after the last chunk has been queued and the host buffer may be reused.
  */

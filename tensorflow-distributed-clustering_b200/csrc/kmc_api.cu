@@ -169,11 +169,31 @@ static int assign_into(kmc_ctx* c, int32_t* labels, cudaStream_t s, int slot = -
     KMC_FAIL(KMC_E_INVALID, "bad kernel path %d", c->path);
 }
 
+// fp64 -> fp32 of a pageable host array straight into a pinned buffer, on several host threads: the rounding is the
+// device's ((float)double, to nearest even), the PCIe copy moves half the bytes and needs no device-side pass
+static void parallel_convert_f64(float* dst, const double* src, size_t count) {
+    const size_t kMin = (size_t)1 << 18;
+    unsigned nt = std::thread::hardware_concurrency();
+    nt = nt == 0 ? 1 : (nt > 16 ? 16 : nt);
+    if (count < 2 * kMin) nt = 1;
+    else if (count / nt < kMin) nt = (unsigned)(count / kMin);
+    auto work = [=](size_t b, size_t e) { for (size_t i = b; i < e; ++i) dst[i] = (float)src[i]; };
+    if (nt <= 1) { work(0, count); return; }
+    std::vector<std::thread> th;
+    const size_t per = (count / nt + 15) & ~(size_t)15;
+    for (unsigned t = 0; t < nt; ++t) {
+        const size_t b = (size_t)t * per;
+        if (b >= count) break;
+        th.emplace_back(work, b, b + per > count ? count : b + per);
+    }
+    for (auto& t : th) t.join();
+}
+
 static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
     const size_t kMin = (size_t)2 << 20;
     if (bytes < 2 * kMin) { memcpy(dst, src, bytes); return; }
     unsigned nt = std::thread::hardware_concurrency();
-    nt = nt == 0 ? 1 : (nt > 8 ? 8 : nt);
+    nt = nt == 0 ? 1 : (nt > 16 ? 16 : nt);
     if (bytes / nt < kMin) nt = (unsigned)(bytes / kMin);
     std::vector<std::thread> th;
     const size_t per = (bytes / nt + 63) & ~(size_t)63;
@@ -413,6 +433,22 @@ int kmc_stage_points(kmc_ctx* c, float* dev_dst, const void* host_src, int src_d
         return 0;
     }
     const int64_t kChunk = kStageChunk;
+    if (!src_pinned && src_dtype == KMC_DTYPE_F64) {
+        // pageable fp64 rows (the reference's callers' arrays): converted to fp32 by the host threads that have to
+        // touch every byte anyway, 64 MB of floats per pinned buffer
+        KMC_TRY(ensure_staging(c, kStageChunk, false));
+        const int64_t per = kChunk / 4;
+        const double* src64 = reinterpret_cast<const double*>(src);
+        int b = 0;
+        for (int64_t e0 = 0; e0 < count; e0 += per, b ^= 1) {
+            const int64_t ne = (count - e0 < per) ? count - e0 : per;
+            KMC_CUDA(cudaEventSynchronize(c->pinned_free[b]));
+            parallel_convert_f64(static_cast<float*>(c->pinned[b]), src64 + e0, (size_t)ne);
+            KMC_CUDA(cudaMemcpyAsync(dev_dst + e0, c->pinned[b], (size_t)ne * 4, cudaMemcpyHostToDevice, s));
+            KMC_CUDA(cudaEventRecord(c->pinned_free[b], s));
+        }
+        return 0;
+    }
     KMC_TRY(ensure_staging(c, kStageChunk, src_dtype == KMC_DTYPE_F64));
     const int64_t elems_per_chunk = kChunk / (int64_t)esz;
     int b = 0;
